@@ -1,0 +1,230 @@
+/*
+ * b200splat — C ABI of the B200-native (sm_100a) differentiable Gaussian-splatting
+ * rasterizer. This is the drop-in boundary: every entry point below is what the
+ * reference's torch binding for this path would bind instead of
+ * CudaRasterizer::Rasterizer (reference file:line cited per function).
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes; no torch / C++ types cross the ABI.
+ *  - Every pointer is a DEVICE pointer borrowed for the duration of the call
+ *    (stream-ordered) unless the name ends in _host. The library never allocates
+ *    or frees device memory; the caller sizes workspaces with the *_workspace_size
+ *    queries and passes them in (the reference instead calls back into three
+ *    std::function<char*(size_t)> allocators, cuda_rasterizer/rasterizer.h:38-40).
+ *  - All kernels are launched on the explicit `stream` (the reference launches on
+ *    the legacy default stream).
+ *  - Return value: 0 = ok; >0 = CUDA error code (cudaError_t) captured with
+ *    cudaGetLastError / cudaStreamSynchronize; <0 = B200S_E_* argument error.
+ *    Nothing throws across the ABI. With args->debug != 0 each stage is followed
+ *    by a stream synchronise + error check (reference CHECK_CUDA,
+ *    cuda_rasterizer/auxiliary.h:166-174).
+ *  - "Absent" optional inputs are NULL (the reference binding passes the data_ptr
+ *    of an empty tensor, which is nullptr: rasterizer_impl.cu:321,389,411).
+ *  - Matrices are 16 floats consumed column-major exactly as the reference does
+ *    (auxiliary.h:58-76): element [i + 4*j] multiplies input component j for
+ *    output component i.
+ */
+#ifndef B200SPLAT_H_INCLUDED
+#define B200SPLAT_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200S_ABI_VERSION 1
+
+/* tile size is fixed by the reference (cuda_rasterizer/config.h:16-17) */
+#define B200S_BLOCK_X 16
+#define B200S_BLOCK_Y 16
+#define B200S_NUM_CHANNELS 3   /* config.h:15 */
+#define B200S_NUM_FEATURES 64  /* rasterizer2 cuda_rasterizer/config.h:3 */
+
+enum {
+    B200S_OK = 0,
+    B200S_E_BADARG = -1,       /* NULL / inconsistent arguments */
+    B200S_E_WORKSPACE = -2,    /* a workspace is smaller than *_workspace_size says */
+    B200S_E_OVERFLOW = -3,     /* num_rendered exceeds the binning capacity */
+    B200S_E_UNSUPPORTED = -4,  /* e.g. SH without 3 channels (rasterizer_impl.cu:242-245) */
+    B200S_E_INTERNAL = -5      /* device-side watchdog tripped (look-back spin bound) */
+};
+
+typedef void* b200s_stream_t; /* cudaStream_t */
+
+/* Header the forward writes at the start of the geometry workspace (device) and
+ * that b200s_read_header copies back. */
+typedef struct B200sHeader {
+    uint32_t num_rendered;   /* sum of tiles_touched == reference's return value */
+    uint32_t overflow;       /* 1 if num_rendered > binning capacity (nothing was binned) */
+    uint32_t error;          /* device-side watchdog flags, 0 when healthy */
+    uint32_t num_visible;    /* Gaussians with radii > 0 */
+    uint32_t reserved[12];
+} B200sHeader;
+
+/* ---- forward: replaces CudaRasterizer::Rasterizer::forward
+ *      (diff-gaussian-rasterization/cuda_rasterizer/rasterizer_impl.cu:198-336) and
+ *      the argument marshalling of RasterizeGaussiansCUDA (rasterize_points.cu:35-115).
+ *      rasterizer2's stripped copy (rasterizer2/.../rasterizer_impl.cu:300-443) is the
+ *      same call with colors_precomp == cov3D_precomp == NULL. */
+typedef struct B200sForwardArgs {
+    int32_t P;               /* number of Gaussians */
+    int32_t D;               /* active SH degree 0..3 */
+    int32_t M;               /* SH coefficients per Gaussian (0 when shs == NULL) */
+    int32_t W, H;            /* image size in pixels */
+    float tan_fovx, tan_fovy;
+    float scale_modifier;
+    int32_t prefiltered;     /* auxiliary.h:156-160: culled-but-prefiltered sets header.error */
+    int32_t debug;
+    const float* background;      /* [3] */
+    const float* means3D;         /* [P,3] */
+    const float* shs;             /* [P,M,3] or NULL */
+    const float* colors_precomp;  /* [P,3] or NULL (exactly one of shs/colors_precomp) */
+    const float* opacities;       /* [P] */
+    const float* scales;          /* [P,3] or NULL */
+    const float* rotations;       /* [P,4] or NULL */
+    const float* cov3D_precomp;   /* [P,6] or NULL (exactly one of scales+rot / cov3D) */
+    const float* viewmatrix;      /* [16] */
+    const float* projmatrix;      /* [16] */
+    const float* campos;          /* [3] */
+    float* out_color;             /* [3,H,W] fully written */
+    int32_t* radii;               /* [P] fully written */
+    void* geom_ws;  size_t geom_bytes;      /* >= b200s_geometry_workspace_size(P) */
+    void* img_ws;   size_t img_bytes;       /* >= b200s_image_workspace_size(W,H) */
+    void* bin_ws;   size_t bin_bytes;       /* >= b200s_binning_workspace_size(capacity,W,H) */
+    int64_t bin_capacity;                   /* instances the binning workspace can hold */
+    int32_t blend_mode;      /* 0 = strict (expf, bit-exact n_contrib); 1 = fast (ex2.approx) */
+    int32_t reserved;
+} B200sForwardArgs;
+
+size_t b200s_geometry_workspace_size(int32_t P);
+size_t b200s_image_workspace_size(int32_t W, int32_t H);
+size_t b200s_binning_workspace_size(int64_t capacity, int32_t W, int32_t H);
+/* Inverse of the above: the capacity a binning workspace of `bytes` bytes was sized for
+ * (lets the backward re-derive the layout from the opaque buffer alone, as the reference
+ * does with BinningState::fromChunk(ptr, R), rasterizer_impl.cu:372). */
+int64_t b200s_binning_capacity_for_bytes(size_t bytes);
+
+/* Stage 1: fused preprocess (cull, EWA covariance/conic, SH, tile rect) + prefix sum.
+ * Leaves header.num_rendered on the device. Never blocks. */
+int b200s_forward_preprocess(const B200sForwardArgs* args, b200s_stream_t stream);
+/* Stage 2: duplicateWithKeys, radix sort, identifyTileRanges, forward blend. Reads
+ * num_rendered from the device; if it exceeds bin_capacity it sets header.overflow and
+ * renders nothing (caller re-runs stage 2 with a larger workspace). Never blocks. */
+int b200s_forward_render(const B200sForwardArgs* args, b200s_stream_t stream);
+/* Both stages back to back. */
+int b200s_forward(const B200sForwardArgs* args, b200s_stream_t stream);
+/* Asynchronous copy of the header into (pinned) host memory. */
+int b200s_read_header(const void* geom_ws, B200sHeader* header_host, b200s_stream_t stream);
+
+/* ---- backward: replaces CudaRasterizer::Rasterizer::backward
+ *      (rasterizer_impl.cu:340-434) and RasterizeGaussiansBackwardCUDA
+ *      (rasterize_points.cu:117-196). The library writes EVERY element of every
+ *      non-NULL output (zeros for culled Gaussians), so the caller may allocate them
+ *      uninitialised — the reference's nine torch::zeros (rasterize_points.cu:151-159)
+ *      are not needed. Optional outputs may be NULL. */
+typedef struct B200sBackwardArgs {
+    int32_t P, D, M, W, H;
+    float tan_fovx, tan_fovy;
+    float scale_modifier;
+    int32_t debug;
+    int32_t deterministic;   /* 1 = fixed-order reduction, bit-reproducible gradients */
+    const float* background;
+    const float* means3D;
+    const float* shs;
+    const float* colors_precomp;
+    const float* opacities;       /* [P] (needed only by the fast blend mode; may be NULL) */
+    const float* scales;
+    const float* rotations;
+    const float* cov3D_precomp;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* campos;
+    const int32_t* radii;         /* [P] from the forward */
+    const float* dL_dout_color;   /* [3,H,W] */
+    const void* geom_ws;  size_t geom_bytes;   /* the forward's workspaces, unmodified */
+    const void* img_ws;   size_t img_bytes;
+    const void* bin_ws;   size_t bin_bytes;
+    int64_t bin_capacity;
+    void* bwd_ws;  size_t bwd_bytes;           /* >= b200s_backward_workspace_size(P, R) */
+    int64_t num_rendered;                      /* R, as returned by the forward */
+    float* dL_dmeans3D;      /* [P,3] */
+    float* dL_dmeans2D;      /* [P,3] (z component is written as 0) */
+    float* dL_dopacity;      /* [P]   */
+    float* dL_dsh;           /* [P,M,3] or NULL */
+    float* dL_dscales;       /* [P,3] or NULL */
+    float* dL_drotations;    /* [P,4] or NULL */
+    float* dL_dcolors;       /* [P,3] or NULL: gradient w.r.t. per-Gaussian RGB */
+    float* dL_dcov3D;        /* [P,6] or NULL */
+    float* dL_dconic;        /* [P,4] or NULL: (a, b, 0, c) as the reference lays it out */
+    int32_t blend_mode;
+    int32_t reserved;
+} B200sBackwardArgs;
+
+size_t b200s_backward_workspace_size(int32_t P, int64_t num_rendered);
+int b200s_backward(const B200sBackwardArgs* args, b200s_stream_t stream);
+
+/* ---- markVisible: replaces Rasterizer::markVisible (rasterizer_impl.cu:141-153) */
+int b200s_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                       const float* projmatrix, uint8_t* present, b200s_stream_t stream);
+
+/* ---- rasterizer2 "idxmap" extra channels: replaces Rasterizer::getidxmap /
+ *      getidxmap_backward (rasterizer2/cuda_rasterizer/rasterizer_impl.cu:851-1008)
+ *      and GetIdxMapCUDA / GetIdxMapBackwardCUDA (rasterizer2/rasterize_points.cu:183-295). */
+typedef struct B200sIdxmapArgs {
+    int32_t P, W, H;
+    int32_t debug;
+    const float* means3D;         /* [P,3] */
+    const float* viewmatrix;      /* [16] */
+    const float* projmatrix;      /* [16] */
+    const float* campos;          /* [3] */
+    const float* feature_vector;  /* [P,64] */
+    int32_t* out_idx;             /* [H,W]    fully written; -1 = no point */
+    float* out_color;             /* [H,W,3]  fully written (zeros where no point) */
+    float* out_depth;             /* [H,W]    fully written */
+    float* out_feature;           /* [H,W,64] fully written */
+    int32_t* radii;               /* [P] 1 if the point's centre is on screen else 0 */
+    void* ws; size_t ws_bytes;    /* >= b200s_idxmap_workspace_size(P,W,H) */
+    uint32_t* num_rendered_dev;   /* optional [1]: sum of clipped footprint areas */
+} B200sIdxmapArgs;
+
+size_t b200s_idxmap_workspace_size(int32_t P, int32_t W, int32_t H);
+int b200s_idxmap_forward(const B200sIdxmapArgs* args, b200s_stream_t stream);
+/* dL_dfeature_vector [P,64] is fully written (zeros + scatter-add of channels 25..63). */
+int b200s_idxmap_backward(int32_t P, int32_t W, int32_t H, const int32_t* out_idx,
+                          const float* grad_feature, float* dL_dfeature_vector,
+                          b200s_stream_t stream);
+
+/* ---- introspection for parity tests: copies one private state array of the last
+ *      forward into a device buffer the caller owns. `which` is a B200S_STATE_* id;
+ *      returns bytes written or a negative error. */
+enum {
+    B200S_STATE_DEPTHS = 0,        /* f32[P]  (0 for culled) */
+    B200S_STATE_MEANS2D = 1,       /* f32[2P] */
+    B200S_STATE_CONIC_OPACITY = 2, /* f32[4P] */
+    B200S_STATE_RGB = 3,           /* f32[3P] */
+    B200S_STATE_TILES_TOUCHED = 4, /* u32[P]  */
+    B200S_STATE_POINT_OFFSETS = 5, /* u32[P]  */
+    B200S_STATE_POINT_LIST = 6,    /* u32[R]  sorted values */
+    B200S_STATE_POINT_LIST_KEYS = 7, /* u64[R] sorted keys */
+    B200S_STATE_RANGES = 8,        /* u32[2*tiles] */
+    B200S_STATE_N_CONTRIB = 9,     /* u32[W*H] */
+    B200S_STATE_FINAL_T = 10,      /* f32[W*H] */
+    B200S_STATE_CLAMPED = 11       /* u8[3P] */
+};
+int64_t b200s_export_state(const B200sForwardArgs* args, int32_t which, int64_t num_rendered,
+                           void* dst, int64_t dst_bytes, b200s_stream_t stream);
+
+/* sizeof() of the ABI structs as compiled: 0 B200sHeader, 1 B200sForwardArgs,
+ * 2 B200sBackwardArgs, 3 B200sIdxmapArgs. Bindings assert their own layout against it. */
+size_t b200s_sizeof(int32_t which);
+
+/* Library / build identification. */
+int b200s_abi_version(void);
+const char* b200s_build_info(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SPLAT_H_INCLUDED */

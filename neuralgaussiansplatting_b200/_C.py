@@ -1,0 +1,331 @@
+"""Drop-in for the reference's pybind `_C` modules, on top of the C ABI (include/b200splat.h).
+
+Same function names, positional arity, argument meaning and return tuples as
+  diff-gaussian-rasterization/ext.cpp:15-19  (rasterize_gaussians, rasterize_gaussians_backward,
+                                              mark_visible; rasterize_points.h:18-67)
+  rasterizer2/ext.cpp:15-20                  (+ get_idxmap2, get_idxmap_backward2;
+                                              rasterize_points.h:53-79)
+so `diff_gaussian_rasterization/__init__.py` and `rasterizer2/__init__.py` read like the
+reference's. PyTorch supplies device memory (caching allocator) and the current stream only.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+NUM_CHANNELS = 3
+NUM_FEATURES = 64
+
+# Opt-in switches (module-level so callers of the reference API need not change signatures).
+#   deterministic: fixed-order gradient reduction (bit-reproducible, no atomics)
+#   optimistic   : size the binning workspace from the previous call of the same shape and
+#                  enqueue the whole forward without the reference's mid-pipeline host sync
+#                  (rasterizer_impl.cu:281); falls back to an exact re-run on overflow.
+config = {"deterministic": False, "optimistic": True, "growth": 1.25}
+
+_tls = threading.local()
+_capacity_hint = {}   # (device index, P, W, H) -> last num_rendered
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32c(t: torch.Tensor, device) -> torch.Tensor:
+    """contiguous float32 on `device` (the reference calls .contiguous().data<float>())."""
+    if t.numel() == 0:
+        return t
+    if t.dtype != torch.float32:
+        raise RuntimeError("expected a float32 tensor")
+    if t.device != device:
+        raise RuntimeError(f"expected tensor on {device}, got {t.device}")
+    t = t.contiguous()
+    if t.data_ptr() % 16:
+        t = t.clone()
+    return t
+
+
+def _stream(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _pinned_header() -> Tuple[torch.Tensor, "_lib.Header"]:
+    buf = getattr(_tls, "hdr", None)
+    if buf is None:
+        buf = torch.zeros(C.sizeof(_lib.Header), dtype=torch.uint8).pin_memory()
+        _tls.hdr = buf
+    return buf, _lib.Header.from_address(buf.data_ptr())
+
+
+def _read_header(lib, geom: torch.Tensor, device) -> "_lib.Header":
+    buf, hdr = _pinned_header()
+    _lib.check(lib.b200s_read_header(geom.data_ptr(), buf.data_ptr(), _stream(device)), "b200s_read_header")
+    torch.cuda.current_stream(device).synchronize()
+    if hdr.error:
+        raise RuntimeError(f"b200splat device error flags 0x{hdr.error:x}"
+                           + (" (point filtered although prefiltered is set)" if hdr.error & 2 else ""))
+    return hdr
+
+
+def _require_cuda(t: torch.Tensor) -> torch.device:
+    if not t.is_cuda:
+        raise RuntimeError("b200splat kernels are CUDA-only (sm_100a); got a CPU tensor and there is no CPU path")
+    return t.device
+
+
+def _fill_forward_args(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                       viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug):
+    dev = means3D.device
+    a = _lib.ForwardArgs()
+    P = means3D.size(0)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    a.P, a.D, a.M, a.W, a.H = P, int(degree), int(M), int(W), int(H)
+    a.tan_fovx, a.tan_fovy, a.scale_modifier = float(tan_fovx), float(tan_fovy), float(scale_modifier)
+    a.prefiltered, a.debug = int(bool(prefiltered)), int(bool(debug))
+    keep = [_f32c(t, dev) for t in (bg, means3D, sh, colors, opacity, scales, rotations, cov3D_precomp,
+                                    viewmatrix, projmatrix, campos)]
+    (a.background, a.means3D, a.shs, a.colors_precomp, a.opacities, a.scales, a.rotations, a.cov3D_precomp,
+     a.viewmatrix, a.projmatrix, a.campos) = [_ptr(t) for t in keep]
+    return a, keep
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                        prefiltered, debug):
+    return _forward_impl(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                         prefiltered, debug)[0]
+
+
+def _forward_impl(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                  viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                  prefiltered, debug):
+    """RasterizeGaussiansCUDA (reference rasterize_points.cu:35-115).
+
+    Returns (num_rendered:int, out_color[3,H,W] f32, radii[P] i32, geomBuffer u8, binningBuffer u8, imgBuffer u8).
+    The three buffers are opaque, as in the reference (their layout is private to the library)."""
+    if means3D.ndimension() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    dev = _require_cuda(means3D)
+    lib = _lib.load()
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    with torch.cuda.device(dev):
+        out_color = torch.empty((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        u8 = dict(dtype=torch.uint8, device=dev)
+        if P == 0:
+            out_color.zero_()
+            return (0, out_color, radii, torch.empty(0, **u8), torch.empty(0, **u8), torch.empty(0, **u8)), None, None
+        a, keep = _fill_forward_args(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                     cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
+                                     campos, prefiltered, debug)
+        geom = torch.empty(lib.b200s_geometry_workspace_size(P), **u8)
+        img = torch.empty(lib.b200s_image_workspace_size(W, H), **u8)
+        a.out_color, a.radii = out_color.data_ptr(), radii.data_ptr()
+        a.geom_ws, a.geom_bytes = geom.data_ptr(), geom.numel()
+        a.img_ws, a.img_bytes = img.data_ptr(), img.numel()
+        stream = _stream(dev)
+
+        def alloc_bin(capacity: int):
+            capacity = max(int(capacity), 1)
+            nbytes = lib.b200s_binning_workspace_size(capacity, W, H)
+            binning = torch.empty(nbytes, **u8)
+            a.bin_ws, a.bin_bytes = binning.data_ptr(), nbytes
+            a.bin_capacity = lib.b200s_binning_capacity_for_bytes(nbytes)
+            return binning
+
+        key = (dev.index, P, W, H)
+        hint = _capacity_hint.get(key) if config["optimistic"] and not debug else None
+        binning = None
+        if hint is not None:
+            binning = alloc_bin(int(hint * config["growth"]) + 4096)
+            _lib.check(lib.b200s_forward(C.byref(a), stream), "b200s_forward")
+            hdr = _read_header(lib, geom, dev)
+            if hdr.overflow:
+                binning = None
+        else:
+            _lib.check(lib.b200s_forward_preprocess(C.byref(a), stream), "b200s_forward_preprocess")
+            hdr = _read_header(lib, geom, dev)
+        num_rendered = int(hdr.num_rendered)
+        if binning is None:
+            binning = alloc_bin(num_rendered)
+            _lib.check(lib.b200s_forward_render(C.byref(a), stream), "b200s_forward_render")
+        _capacity_hint[key] = num_rendered
+    return (num_rendered, out_color, radii, geom, binning, img), a, keep
+
+
+def _backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                   projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer,
+                   imageBuffer, debug, want_all: bool):
+    dev = _require_cuda(means3D)
+    lib = _lib.load()
+    P = means3D.size(0)
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        has_sh = sh.numel() != 0
+        has_sr = scales.numel() != 0
+        g_means3D = torch.empty((P, 3), **f32)
+        g_means2D = torch.empty((P, 3), **f32)
+        g_opacity = torch.empty((P, 1), **f32)
+        g_sh = torch.empty((P, M, 3), **f32) if has_sh else torch.zeros((P, M, 3), **f32)
+        g_scales = torch.empty((P, 3), **f32) if has_sr else torch.zeros((P, 3), **f32)
+        g_rot = torch.empty((P, 4), **f32) if has_sr else torch.zeros((P, 4), **f32)
+        g_colors = torch.empty((P, NUM_CHANNELS), **f32) if (want_all or not has_sh) else None
+        g_cov3D = torch.empty((P, 6), **f32) if (want_all or not has_sr) else None
+        if P == 0:
+            return g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot
+        a = _lib.BackwardArgs()
+        a.P, a.D, a.M, a.W, a.H = P, int(degree), int(M), int(W), int(H)
+        a.tan_fovx, a.tan_fovy, a.scale_modifier = float(tan_fovx), float(tan_fovy), float(scale_modifier)
+        a.debug = int(bool(debug))
+        a.deterministic = int(bool(config["deterministic"]))
+        keep = [_f32c(t, dev) for t in (background, means3D, sh, colors, scales, rotations, cov3D_precomp, viewmatrix,
+                                        projmatrix, campos, dL_dout_color)]
+        (a.background, a.means3D, a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp, a.viewmatrix,
+         a.projmatrix, a.campos, a.dL_dout_color) = [_ptr(t) for t in keep]
+        radii_c = radii.contiguous()
+        a.radii = radii_c.data_ptr()
+        a.geom_ws, a.geom_bytes = geomBuffer.data_ptr(), geomBuffer.numel()
+        a.img_ws, a.img_bytes = imageBuffer.data_ptr(), imageBuffer.numel()
+        a.bin_ws, a.bin_bytes = _ptr(binningBuffer), binningBuffer.numel()
+        a.bin_capacity = lib.b200s_binning_capacity_for_bytes(binningBuffer.numel()) if binningBuffer.numel() else 0
+        a.num_rendered = int(R)
+        nbytes = lib.b200s_backward_workspace_size(P, int(R) if a.deterministic else 0)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        a.bwd_ws, a.bwd_bytes = ws.data_ptr(), nbytes
+        a.dL_dmeans3D, a.dL_dmeans2D, a.dL_dopacity = g_means3D.data_ptr(), g_means2D.data_ptr(), g_opacity.data_ptr()
+        a.dL_dsh = g_sh.data_ptr() if has_sh else None
+        a.dL_dscales = g_scales.data_ptr() if has_sr else None
+        a.dL_drotations = g_rot.data_ptr() if has_sr else None
+        a.dL_dcolors = g_colors.data_ptr() if g_colors is not None else None
+        a.dL_dcov3D = g_cov3D.data_ptr() if g_cov3D is not None else None
+        _lib.check(lib.b200s_backward(C.byref(a), _stream(dev)), "b200s_backward")
+        del keep
+    return g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                 cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree,
+                                 campos, geomBuffer, R, binningBuffer, imageBuffer, debug):
+    """RasterizeGaussiansBackwardCUDA (reference rasterize_points.cu:117-196).
+
+    Returns (dL_dmeans2D[P,3], dL_dcolors[P,3], dL_dopacity[P,1], dL_dmeans3D[P,3], dL_dcov3D[P,6],
+             dL_dsh[P,M,3], dL_dscales[P,3], dL_drotations[P,4])."""
+    return _backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                          viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer,
+                          R, binningBuffer, imageBuffer, debug, want_all=True)
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """markVisible (reference rasterize_points.cu:198-217): bool[P] near-plane frustum mask."""
+    dev = _require_cuda(means3D)
+    lib = _lib.load()
+    P = means3D.size(0)
+    with torch.cuda.device(dev):
+        present = torch.zeros((P,), dtype=torch.bool, device=dev)
+        if P != 0:
+            m, v, pj = _f32c(means3D, dev), _f32c(viewmatrix, dev), _f32c(projmatrix, dev)
+            _lib.check(lib.b200s_mark_visible(P, m.data_ptr(), v.data_ptr(), pj.data_ptr(), present.data_ptr(),
+                                              _stream(dev)), "b200s_mark_visible")
+    return present
+
+
+def get_idxmap2(background, means3D, normal, scales, rotations, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                image_height, image_width, feature_vector, sh, campos, debug):
+    """GetIdxMapCUDA (reference rasterizer2/rasterize_points.cu:183-260).
+
+    Returns (num_rendered:int, out_idx[H,W] i32, out_color[H,W,3], out_depth[H,W], out_feature[H,W,64]).
+    `background`, `normal`, `scales`, `rotations`, `sh`, `tan_fov*` are accepted and unused, exactly as the
+    reference kernels leave them unused (rasterizer_impl.cu:731-817)."""
+    dev = _require_cuda(means3D)
+    lib = _lib.load()
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    with torch.cuda.device(dev):
+        f32 = dict(dtype=torch.float32, device=dev)
+        out_idx = torch.empty((H, W), dtype=torch.int32, device=dev)
+        out_color = torch.empty((H, W, NUM_CHANNELS), **f32)
+        out_depth = torch.empty((H, W), **f32)
+        out_feature = torch.empty((H, W, NUM_FEATURES), **f32)
+        radii = torch.empty((max(P, 1),), dtype=torch.int32, device=dev)
+        nr = torch.zeros((1,), dtype=torch.int32, device=dev)
+        a = _lib.IdxmapArgs()
+        a.P, a.W, a.H, a.debug = P, W, H, int(bool(debug))
+        keep = [_f32c(t, dev) for t in (means3D, viewmatrix, projmatrix, campos, feature_vector)]
+        a.means3D, a.viewmatrix, a.projmatrix, a.campos, a.feature_vector = [_ptr(t) for t in keep]
+        a.out_idx, a.out_color, a.out_depth, a.out_feature = (out_idx.data_ptr(), out_color.data_ptr(),
+                                                              out_depth.data_ptr(), out_feature.data_ptr())
+        a.radii = radii.data_ptr()
+        nbytes = lib.b200s_idxmap_workspace_size(P, W, H)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        a.ws, a.ws_bytes = ws.data_ptr(), nbytes
+        a.num_rendered_dev = nr.data_ptr()
+        _lib.check(lib.b200s_idxmap_forward(C.byref(a), _stream(dev)), "b200s_idxmap_forward")
+        num_rendered = int(nr.item())   # the reference returns it as a host int (blocking D2H, :923)
+        del keep
+    return num_rendered, out_idx, out_color, out_depth, out_feature
+
+
+def get_idxmap_backward2(means3D, image_height, image_width, campos, out_idx, grad_feature, debug):
+    """GetIdxMapBackwardCUDA (reference rasterizer2/rasterize_points.cu:262-295) -> (dL_dfeature_vector[P,64],)"""
+    dev = _require_cuda(means3D)
+    lib = _lib.load()
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    with torch.cuda.device(dev):
+        grad = torch.empty((P, NUM_FEATURES), dtype=torch.float32, device=dev)
+        if P != 0:
+            idx = out_idx.contiguous()
+            gf = _f32c(grad_feature, dev)
+            _lib.check(lib.b200s_idxmap_backward(P, W, H, idx.data_ptr(), gf.data_ptr(), grad.data_ptr(), _stream(dev)),
+                       "b200s_idxmap_backward")
+    return (grad,)
+
+
+_STATE_DTYPES = {
+    "depths": (torch.float32, lambda P, R, T, px: (P,)),
+    "means2D": (torch.float32, lambda P, R, T, px: (P, 2)),
+    "conic_opacity": (torch.float32, lambda P, R, T, px: (P, 4)),
+    "rgb": (torch.float32, lambda P, R, T, px: (P, 3)),
+    "tiles_touched": (torch.int32, lambda P, R, T, px: (P,)),
+    "point_offsets": (torch.int32, lambda P, R, T, px: (P,)),
+    "point_list": (torch.int32, lambda P, R, T, px: (R,)),
+    "point_list_keys": (torch.int64, lambda P, R, T, px: (R,)),
+    "ranges": (torch.int32, lambda P, R, T, px: (T, 2)),
+    "n_contrib": (torch.int32, lambda P, R, T, px: (px,)),
+    "final_T": (torch.float32, lambda P, R, T, px: (px,)),
+    "clamped": (torch.uint8, lambda P, R, T, px: (P, 3)),
+}
+
+
+def forward_with_state(*args, names=None):
+    """Parity-test helper: rasterize_gaussians(*args) plus a dict of the library's private state
+    arrays (re-exported in the reference's layouts through b200s_export_state)."""
+    out, a, keep = _forward_impl(*args)
+    state = {}
+    if a is None:
+        return out, state
+    lib = _lib.load()
+    num_rendered, out_color, radii, geom, binning, img = out
+    dev = out_color.device
+    P, W, H = a.P, a.W, a.H
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    with torch.cuda.device(dev):
+        for name in (names or _STATE_DTYPES):
+            dtype, shape = _STATE_DTYPES[name]
+            t = torch.zeros(shape(P, num_rendered, T, W * H), dtype=dtype, device=dev)
+            nbytes = t.numel() * t.element_size()
+            rc = lib.b200s_export_state(C.byref(a), _lib.STATE[name], num_rendered, t.data_ptr() if nbytes else None,
+                                        nbytes, _stream(dev)) if nbytes else 0
+            if rc < 0:
+                raise RuntimeError(f"b200s_export_state({name}) failed: {rc}")
+            state[name] = t
+        torch.cuda.current_stream(dev).synchronize()
+    return out, state

@@ -1,0 +1,152 @@
+"""ctypes binding of libb200splat.so — the C ABI declared in include/b200splat.h.
+
+There is no CPU or PyTorch fallback: if the shared library is missing it is built in-tree
+with nvcc (see build.py); if that is impossible the import fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+from . import build as _build
+
+c_f32p = C.c_void_p  # device pointers are passed as integers
+
+
+class Header(C.Structure):
+    _fields_ = [
+        ("num_rendered", C.c_uint32),
+        ("overflow", C.c_uint32),
+        ("error", C.c_uint32),
+        ("num_visible", C.c_uint32),
+        ("reserved", C.c_uint32 * 12),
+    ]
+
+
+class ForwardArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("W", C.c_int32), ("H", C.c_int32),
+        ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("scale_modifier", C.c_float),
+        ("prefiltered", C.c_int32), ("debug", C.c_int32),
+        ("background", C.c_void_p), ("means3D", C.c_void_p), ("shs", C.c_void_p),
+        ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p), ("scales", C.c_void_p),
+        ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p), ("viewmatrix", C.c_void_p),
+        ("projmatrix", C.c_void_p), ("campos", C.c_void_p),
+        ("out_color", C.c_void_p), ("radii", C.c_void_p),
+        ("geom_ws", C.c_void_p), ("geom_bytes", C.c_size_t),
+        ("img_ws", C.c_void_p), ("img_bytes", C.c_size_t),
+        ("bin_ws", C.c_void_p), ("bin_bytes", C.c_size_t),
+        ("bin_capacity", C.c_int64),
+        ("blend_mode", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class BackwardArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("W", C.c_int32), ("H", C.c_int32),
+        ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("scale_modifier", C.c_float),
+        ("debug", C.c_int32), ("deterministic", C.c_int32),
+        ("background", C.c_void_p), ("means3D", C.c_void_p), ("shs", C.c_void_p),
+        ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p), ("scales", C.c_void_p),
+        ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p), ("viewmatrix", C.c_void_p),
+        ("projmatrix", C.c_void_p), ("campos", C.c_void_p), ("radii", C.c_void_p),
+        ("dL_dout_color", C.c_void_p),
+        ("geom_ws", C.c_void_p), ("geom_bytes", C.c_size_t),
+        ("img_ws", C.c_void_p), ("img_bytes", C.c_size_t),
+        ("bin_ws", C.c_void_p), ("bin_bytes", C.c_size_t),
+        ("bin_capacity", C.c_int64),
+        ("bwd_ws", C.c_void_p), ("bwd_bytes", C.c_size_t),
+        ("num_rendered", C.c_int64),
+        ("dL_dmeans3D", C.c_void_p), ("dL_dmeans2D", C.c_void_p), ("dL_dopacity", C.c_void_p),
+        ("dL_dsh", C.c_void_p), ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p),
+        ("dL_dcolors", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dconic", C.c_void_p),
+        ("blend_mode", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class IdxmapArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("W", C.c_int32), ("H", C.c_int32), ("debug", C.c_int32),
+        ("means3D", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p),
+        ("campos", C.c_void_p), ("feature_vector", C.c_void_p),
+        ("out_idx", C.c_void_p), ("out_color", C.c_void_p), ("out_depth", C.c_void_p),
+        ("out_feature", C.c_void_p), ("radii", C.c_void_p),
+        ("ws", C.c_void_p), ("ws_bytes", C.c_size_t),
+        ("num_rendered_dev", C.c_void_p),
+    ]
+
+
+STATE = {
+    "depths": 0, "means2D": 1, "conic_opacity": 2, "rgb": 3, "tiles_touched": 4, "point_offsets": 5,
+    "point_list": 6, "point_list_keys": 7, "ranges": 8, "n_contrib": 9, "final_T": 10, "clamped": 11,
+}
+
+ERRORS = {
+    -1: "B200S_E_BADARG (NULL or inconsistent arguments)",
+    -2: "B200S_E_WORKSPACE (workspace smaller than required)",
+    -3: "B200S_E_OVERFLOW (num_rendered exceeds the binning capacity)",
+    -4: "B200S_E_UNSUPPORTED",
+    -5: "B200S_E_INTERNAL (device watchdog)",
+}
+
+# every symbol include/b200splat.h declares: (name, restype, argtypes)
+SYMBOLS = [
+    ("b200s_abi_version", C.c_int, []),
+    ("b200s_build_info", C.c_char_p, []),
+    ("b200s_sizeof", C.c_size_t, [C.c_int32]),
+    ("b200s_geometry_workspace_size", C.c_size_t, [C.c_int32]),
+    ("b200s_image_workspace_size", C.c_size_t, [C.c_int32, C.c_int32]),
+    ("b200s_binning_workspace_size", C.c_size_t, [C.c_int64, C.c_int32, C.c_int32]),
+    ("b200s_binning_capacity_for_bytes", C.c_int64, [C.c_size_t]),
+    ("b200s_backward_workspace_size", C.c_size_t, [C.c_int32, C.c_int64]),
+    ("b200s_forward_preprocess", C.c_int, [C.POINTER(ForwardArgs), C.c_void_p]),
+    ("b200s_forward_render", C.c_int, [C.POINTER(ForwardArgs), C.c_void_p]),
+    ("b200s_forward", C.c_int, [C.POINTER(ForwardArgs), C.c_void_p]),
+    ("b200s_read_header", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    ("b200s_backward", C.c_int, [C.POINTER(BackwardArgs), C.c_void_p]),
+    ("b200s_mark_visible", C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ("b200s_idxmap_workspace_size", C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
+    ("b200s_idxmap_forward", C.c_int, [C.POINTER(IdxmapArgs), C.c_void_p]),
+    ("b200s_idxmap_backward", C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ("b200s_export_state", C.c_int64, [C.POINTER(ForwardArgs), C.c_int32, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
+]
+
+_lib = None
+
+
+def lib_path() -> Path:
+    return _build.LIB_PATH
+
+
+def load() -> C.CDLL:
+    """Load (building first if needed) the shared library and bind every declared symbol."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not path.exists() or os.environ.get("B200S_REBUILD"):
+        _build.build(force=bool(os.environ.get("B200S_REBUILD")))
+    if not path.exists():
+        raise RuntimeError(f"{path} is missing and could not be built; b200splat has no fallback path")
+    lib = C.CDLL(str(path))
+    for name, restype, argtypes in SYMBOLS:
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = restype
+        fn.argtypes = argtypes
+    if lib.b200s_abi_version() != 1:
+        raise RuntimeError("libb200splat.so ABI version mismatch")
+    for which, struct in enumerate((Header, ForwardArgs, BackwardArgs, IdxmapArgs)):
+        if lib.b200s_sizeof(which) != C.sizeof(struct):
+            raise RuntimeError(f"ctypes layout of {struct.__name__} does not match the library")
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str) -> None:
+    """Non-zero status -> RuntimeError (the reference binding throws std::runtime_error)."""
+    if rc == 0:
+        return
+    if rc < 0:
+        raise RuntimeError(f"{what}: {ERRORS.get(rc, rc)}")
+    raise RuntimeError(f"{what}: CUDA error {rc}")

@@ -1,0 +1,337 @@
+// extern "C" entry points of libb200splat.so (see include/b200splat.h).
+// Host orchestration only: carves the caller's workspaces and enqueues the kernels on the
+// caller's stream. Replaces CudaRasterizer::Rasterizer::{forward,backward,markVisible}
+// (reference rasterizer_impl.cu:141-153,198-434).
+
+#include <cstdlib>
+#include <cstring>
+#include "kernels.cuh"
+
+using namespace b200s;
+
+namespace b200s {
+int idxmap_forward_impl(const B200sIdxmapArgs* a, cudaStream_t stream);
+int idxmap_backward_impl(int P, int W, int H, const int32_t* out_idx, const float* grad_feature,
+                         float* dL_dfeature_vector, cudaStream_t stream);
+size_t idxmap_workspace_size_impl(int P, int W, int H);
+}
+
+namespace {
+
+// Warps per tile for the blend kernels; overridable for tuning (B200S_BLEND_WARPS=1|2|4|8).
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    if (!v || !*v) return dflt;
+    return atoi(v);
+}
+int blend_fwd_warps() { static int v = env_int("B200S_BLEND_FWD_WARPS", 4); return v; }
+int blend_bwd_warps() { static int v = env_int("B200S_BLEND_BWD_WARPS", 4); return v; }
+
+struct Dims { int gx, gy, tiles; float focal_x, focal_y; };
+Dims dims_of(int W, int H, float tan_fovx, float tan_fovy) {
+    Dims d;
+    d.gx = (W + TILE - 1) / TILE;
+    d.gy = (H + TILE - 1) / TILE;
+    d.tiles = d.gx * d.gy;
+    // rasterizer_impl.cu:222-223 (host float arithmetic)
+    d.focal_y = H / (2.0f * tan_fovy);
+    d.focal_x = W / (2.0f * tan_fovx);
+    return d;
+}
+
+int check_forward_args(const B200sForwardArgs* a) {
+    if (!a) return B200S_E_BADARG;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0) return B200S_E_BADARG;
+    if (a->P == 0) return 0;
+    if (!a->means3D || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->campos || !a->background)
+        return B200S_E_BADARG;
+    if (!a->out_color || !a->radii) return B200S_E_BADARG;
+    if ((a->shs == nullptr) == (a->colors_precomp == nullptr)) return B200S_E_BADARG;
+    const bool has_sr = a->scales != nullptr && a->rotations != nullptr;
+    if (has_sr == (a->cov3D_precomp != nullptr)) return B200S_E_BADARG;
+    if (a->shs && a->M <= 0) return B200S_E_BADARG;
+    if (a->W > 65535 * TILE || a->H > 65535 * TILE) return B200S_E_UNSUPPORTED;
+    if (!a->geom_ws || !a->img_ws) return B200S_E_BADARG;
+    if (a->geom_bytes < b200s_geometry_workspace_size(a->P)) return B200S_E_WORKSPACE;
+    if (a->img_bytes < b200s_image_workspace_size(a->W, a->H)) return B200S_E_WORKSPACE;
+    if (a->rotations && (reinterpret_cast<uintptr_t>(a->rotations) & 15)) return B200S_E_BADARG;
+    if ((reinterpret_cast<uintptr_t>(a->geom_ws) & 255) || (reinterpret_cast<uintptr_t>(a->img_ws) & 255))
+        return B200S_E_BADARG;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200s_abi_version(void) { return B200S_ABI_VERSION; }
+
+const char* b200s_build_info(void) {
+    return "b200splat sm_100a nvcc " __DATE__ " " __TIME__;
+}
+
+size_t b200s_geometry_workspace_size(int32_t P) {
+    return carve_geom(nullptr, P > 0 ? P : 1).bytes;
+}
+size_t b200s_image_workspace_size(int32_t W, int32_t H) {
+    return carve_img(nullptr, W, H).bytes;
+}
+size_t b200s_binning_workspace_size(int64_t capacity, int32_t W, int32_t H) {
+    (void)W; (void)H;
+    return carve_bin(nullptr, capacity).bytes;
+}
+size_t b200s_backward_workspace_size(int32_t P, int64_t num_rendered) {
+    return carve_bwd(nullptr, P, num_rendered).bytes;
+}
+int64_t b200s_binning_capacity_for_bytes(size_t bytes) {
+    // largest capacity whose workspace fits in `bytes` (sizes are monotone in capacity, and equal
+    // sizes imply identical internal offsets, so this inverts b200s_binning_workspace_size)
+    int64_t lo = 0, hi = (1ll << 30) - 1;
+    if (carve_bin(nullptr, 1).bytes > bytes) return -1;
+    while (lo < hi) {
+        const int64_t mid = lo + (hi - lo + 1) / 2;
+        if (carve_bin(nullptr, mid).bytes <= bytes) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+size_t b200s_sizeof(int32_t which) {
+    switch (which) {
+        case 0: return sizeof(B200sHeader);
+        case 1: return sizeof(B200sForwardArgs);
+        case 2: return sizeof(B200sBackwardArgs);
+        case 3: return sizeof(B200sIdxmapArgs);
+        default: return 0;
+    }
+}
+
+int b200s_forward_preprocess(const B200sForwardArgs* a, b200s_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int rc = check_forward_args(a);
+    if (rc) return rc;
+    const Dims d = dims_of(a->W, a->H, a->tan_fovx, a->tan_fovy);
+    GeomWS g = carve_geom(a->geom_ws, a->P > 0 ? a->P : 1);
+    // header + counters + scan status are small; clear them every call
+    B200S_CUDA_OK(cudaMemsetAsync(g.header, 0, sizeof(B200sHeader), stream));
+    B200S_CUDA_OK(cudaMemsetAsync(g.counters, 0, 64 * sizeof(uint32_t), stream));
+    if (a->P == 0) return 0;
+    B200S_CUDA_OK(cudaMemsetAsync(g.scan_status, 0, 4 * ((size_t)(a->P + SCAN_TILE - 1) / SCAN_TILE + 1), stream));
+    PreprocessParams p;
+    p.P = a->P; p.D = a->D; p.M = a->M; p.W = a->W; p.H = a->H;
+    p.grid_x = d.gx; p.grid_y = d.gy;
+    p.tan_fovx = a->tan_fovx; p.tan_fovy = a->tan_fovy; p.focal_x = d.focal_x; p.focal_y = d.focal_y;
+    p.scale_modifier = a->scale_modifier; p.prefiltered = a->prefiltered;
+    p.means3D = a->means3D; p.shs = a->shs; p.colors_precomp = a->colors_precomp; p.opacities = a->opacities;
+    p.scales = a->scales; p.rotations = a->rotations; p.cov3D_precomp = a->cov3D_precomp;
+    p.viewmatrix = a->viewmatrix; p.projmatrix = a->projmatrix; p.campos = a->campos;
+    p.radii = a->radii; p.rec = g.rec; p.tiles_touched = g.tiles_touched; p.clamped = g.clamped;
+    p.header = g.header; p.counters = g.counters;
+    rc = launch_preprocess_fwd(p, stream);
+    if (rc) return rc;
+    B200S_AFTER_LAUNCH(stream, a->debug);
+    rc = launch_scan(g.tiles_touched, g.point_offsets, a->P, g.scan_status, g.counters, g.header, stream);
+    if (rc) return rc;
+    B200S_AFTER_LAUNCH(stream, a->debug);
+    return 0;
+}
+
+int b200s_forward_render(const B200sForwardArgs* a, b200s_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int rc = check_forward_args(a);
+    if (rc) return rc;
+    const Dims d = dims_of(a->W, a->H, a->tan_fovx, a->tan_fovy);
+    const size_t plane = (size_t)a->W * a->H;
+    if (a->P == 0) {
+        // RasterizeGaussiansCUDA returns the zero-initialised image when P == 0
+        // (rasterize_points.cu:68,80): keep that.
+        B200S_CUDA_OK(cudaMemsetAsync(a->out_color, 0, 3 * plane * sizeof(float), stream));
+        return 0;
+    }
+    if (!a->bin_ws || a->bin_capacity < 0) return B200S_E_BADARG;
+    if (reinterpret_cast<uintptr_t>(a->bin_ws) & 255) return B200S_E_BADARG;
+    if (a->bin_bytes < b200s_binning_workspace_size(a->bin_capacity, a->W, a->H)) return B200S_E_WORKSPACE;
+    if (a->bin_capacity >= (1ll << 30)) return B200S_E_UNSUPPORTED;
+    GeomWS g = carve_geom(a->geom_ws, a->P);
+    ImgWS im = carve_img(a->img_ws, a->W, a->H);
+    BinWS bw = carve_bin(a->bin_ws, a->bin_capacity);
+    int final_buf = 0;
+    // stage 2 may be re-run with a larger workspace after an overflow: reset its device state
+    B200S_CUDA_OK(cudaMemsetAsync(&g.header->overflow, 0, sizeof(uint32_t), stream));
+    B200S_CUDA_OK(cudaMemsetAsync(g.counters + CTR_SORT_TICKET0, 0, SORT_MAX_PASSES * sizeof(uint32_t), stream));
+    rc = launch_binning(a->P, g.rec, g.point_offsets, bw, a->bin_capacity, a->bin_capacity, d.gx, d.tiles,
+                        im.ranges, g.header, g.counters, &final_buf, a->debug != 0, stream);
+    if (rc) return rc;
+    BlendFwdParams b;
+    b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;
+    b.ranges = im.ranges; b.point_list = bw.vals[final_buf]; b.rec = g.rec; b.background = a->background;
+    b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last; b.out_color = a->out_color;
+    rc = launch_blend_fwd(b, blend_fwd_warps(), stream);
+    if (rc) return rc;
+    B200S_AFTER_LAUNCH(stream, a->debug);
+    return 0;
+}
+
+int b200s_forward(const B200sForwardArgs* a, b200s_stream_t stream) {
+    int rc = b200s_forward_preprocess(a, stream);
+    if (rc) return rc;
+    return b200s_forward_render(a, stream);
+}
+
+int b200s_read_header(const void* geom_ws, B200sHeader* header_host, b200s_stream_t stream) {
+    if (!geom_ws || !header_host) return B200S_E_BADARG;
+    B200S_CUDA_OK(cudaMemcpyAsync(header_host, geom_ws, sizeof(B200sHeader), cudaMemcpyDeviceToHost,
+                                  (cudaStream_t)stream));
+    return 0;
+}
+
+int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!a) return B200S_E_BADARG;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0) return B200S_E_BADARG;
+    if (a->P == 0) return 0;
+    if (!a->means3D || !a->viewmatrix || !a->projmatrix || !a->campos || !a->background || !a->radii ||
+        !a->dL_dout_color || !a->geom_ws || !a->img_ws || !a->bwd_ws)
+        return B200S_E_BADARG;
+    if (!a->dL_dmeans3D || !a->dL_dmeans2D || !a->dL_dopacity) return B200S_E_BADARG;
+    if ((a->shs == nullptr) == (a->colors_precomp == nullptr)) return B200S_E_BADARG;
+    const bool has_sr = a->scales != nullptr && a->rotations != nullptr;
+    if (has_sr == (a->cov3D_precomp != nullptr)) return B200S_E_BADARG;
+    if (a->num_rendered < 0 || a->num_rendered > a->bin_capacity) return B200S_E_BADARG;
+    if (a->num_rendered > 0 && !a->bin_ws) return B200S_E_BADARG;
+    if (a->bwd_bytes < b200s_backward_workspace_size(a->P, a->deterministic ? a->num_rendered : 0))
+        return B200S_E_WORKSPACE;
+    if (a->dL_drotations && (reinterpret_cast<uintptr_t>(a->dL_drotations) & 15)) return B200S_E_BADARG;
+    if (a->dL_dconic && (reinterpret_cast<uintptr_t>(a->dL_dconic) & 15)) return B200S_E_BADARG;
+    if (reinterpret_cast<uintptr_t>(a->bwd_ws) & 255) return B200S_E_BADARG;
+
+    const Dims d = dims_of(a->W, a->H, a->tan_fovx, a->tan_fovy);
+    GeomWS g = carve_geom(const_cast<void*>(a->geom_ws), a->P);
+    ImgWS im = carve_img(const_cast<void*>(a->img_ws), a->W, a->H);
+    BinWS bw = carve_bin(const_cast<void*>(a->bin_ws), a->bin_capacity);
+    BwdWS ws = carve_bwd(a->bwd_ws, a->P, a->deterministic ? a->num_rendered : 0);
+    const int passes = sort_num_passes(d.tiles);
+    const int final_buf = passes & 1;
+
+    if (a->deterministic) {
+        B200S_CUDA_OK(cudaMemsetAsync(ws.partial, 0, sizeof(float) * ACC_STRIDE * (size_t)(a->num_rendered > 0 ? a->num_rendered : 1), stream));
+    } else {
+        B200S_CUDA_OK(cudaMemsetAsync(ws.accum, 0, sizeof(float) * ACC_STRIDE * (size_t)a->P, stream));
+    }
+    if (a->num_rendered > 0) {
+        BlendBwdParams b;
+        b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;
+        b.ranges = im.ranges; b.point_list = bw.vals[final_buf]; b.rec = g.rec; b.point_offsets = g.point_offsets;
+        b.background = a->background; b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last;
+        b.dL_dpix = a->dL_dout_color; b.accum = ws.accum; b.partial = ws.partial; b.deterministic = a->deterministic;
+        int rc = launch_blend_bwd(b, blend_bwd_warps(), stream);
+        if (rc) return rc;
+        B200S_AFTER_LAUNCH(stream, a->debug);
+    }
+    PreprocessBwdParams p;
+    p.P = a->P; p.D = a->D; p.M = a->M; p.W = a->W; p.H = a->H;
+    p.tan_fovx = a->tan_fovx; p.tan_fovy = a->tan_fovy; p.focal_x = d.focal_x; p.focal_y = d.focal_y;
+    p.scale_modifier = a->scale_modifier;
+    p.means3D = a->means3D; p.shs = a->shs; p.colors_precomp = a->colors_precomp; p.scales = a->scales;
+    p.rotations = a->rotations; p.cov3D_precomp = a->cov3D_precomp; p.viewmatrix = a->viewmatrix;
+    p.projmatrix = a->projmatrix; p.campos = a->campos; p.radii = a->radii; p.rec = g.rec; p.clamped = g.clamped;
+    p.point_offsets = g.point_offsets;
+    p.accum = a->deterministic ? nullptr : ws.accum;
+    p.partial = a->deterministic ? ws.partial : nullptr;
+    p.dL_dmeans3D = a->dL_dmeans3D; p.dL_dmeans2D = a->dL_dmeans2D; p.dL_dopacity = a->dL_dopacity;
+    p.dL_dsh = a->dL_dsh; p.dL_dscales = a->dL_dscales; p.dL_drotations = a->dL_drotations;
+    p.dL_dcolors = a->dL_dcolors; p.dL_dcov3D = a->dL_dcov3D; p.dL_dconic = a->dL_dconic;
+    int rc = launch_preprocess_bwd(p, stream);
+    if (rc) return rc;
+    B200S_AFTER_LAUNCH(stream, a->debug);
+    return 0;
+}
+
+int b200s_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                       uint8_t* present, b200s_stream_t stream) {
+    (void)projmatrix;   // the reference's in_frustum only tests view-space depth (auxiliary.h:154)
+    if (P < 0) return B200S_E_BADARG;
+    if (P == 0) return 0;
+    if (!means3D || !viewmatrix || !present) return B200S_E_BADARG;
+    return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+}
+
+size_t b200s_idxmap_workspace_size(int32_t P, int32_t W, int32_t H) {
+    return idxmap_workspace_size_impl(P, W, H);
+}
+int b200s_idxmap_forward(const B200sIdxmapArgs* args, b200s_stream_t stream) {
+    return idxmap_forward_impl(args, (cudaStream_t)stream);
+}
+int b200s_idxmap_backward(int32_t P, int32_t W, int32_t H, const int32_t* out_idx, const float* grad_feature,
+                          float* dL_dfeature_vector, b200s_stream_t stream) {
+    return idxmap_backward_impl(P, W, H, out_idx, grad_feature, dL_dfeature_vector, (cudaStream_t)stream);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------- state export
+namespace {
+__global__ void export_rec_kernel(int P, const SplatRec* rec, const int* radii, const uint8_t* clamped, int which,
+                                  float* dst_f, uint8_t* dst_b) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const bool vis = radii[i] > 0;
+    SplatRec r;
+    r.q0 = r.q1 = r.q2 = make_float4(0, 0, 0, 0);
+    if (vis) r = rec[i];
+    switch (which) {
+        case B200S_STATE_DEPTHS: dst_f[i] = r.q2.y; break;
+        case B200S_STATE_MEANS2D: dst_f[2 * i] = r.q0.x; dst_f[2 * i + 1] = r.q0.y; break;
+        case B200S_STATE_CONIC_OPACITY:
+            dst_f[4 * i] = r.q0.z; dst_f[4 * i + 1] = r.q0.w; dst_f[4 * i + 2] = r.q1.x; dst_f[4 * i + 3] = r.q1.y; break;
+        case B200S_STATE_RGB: dst_f[3 * i] = r.q1.z; dst_f[3 * i + 1] = r.q1.w; dst_f[3 * i + 2] = r.q2.x; break;
+        case B200S_STATE_CLAMPED: {
+            const uint8_t c = vis ? clamped[i] : 0;
+            dst_b[3 * i] = c & 1; dst_b[3 * i + 1] = (c >> 1) & 1; dst_b[3 * i + 2] = (c >> 2) & 1; break;
+        }
+    }
+}
+}  // namespace
+
+extern "C" int64_t b200s_export_state(const B200sForwardArgs* a, int32_t which, int64_t num_rendered, void* dst,
+                                      int64_t dst_bytes, b200s_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!a || !dst) return B200S_E_BADARG;
+    const int64_t P = a->P;
+    const Dims d = dims_of(a->W, a->H, a->tan_fovx, a->tan_fovy);
+    GeomWS g = carve_geom(a->geom_ws, P > 0 ? P : 1);
+    ImgWS im = carve_img(a->img_ws, a->W, a->H);
+    const int64_t px = (int64_t)a->W * a->H;
+    const void* src = nullptr;
+    int64_t bytes = 0;
+    switch (which) {
+        case B200S_STATE_DEPTHS: bytes = 4 * P; break;
+        case B200S_STATE_MEANS2D: bytes = 8 * P; break;
+        case B200S_STATE_CONIC_OPACITY: bytes = 16 * P; break;
+        case B200S_STATE_RGB: bytes = 12 * P; break;
+        case B200S_STATE_CLAMPED: bytes = 3 * P; break;
+        case B200S_STATE_TILES_TOUCHED: src = g.tiles_touched; bytes = 4 * P; break;
+        case B200S_STATE_POINT_OFFSETS: src = g.point_offsets; bytes = 4 * P; break;
+        case B200S_STATE_RANGES: src = im.ranges; bytes = 8 * (int64_t)d.tiles; break;
+        case B200S_STATE_N_CONTRIB: src = im.n_contrib; bytes = 4 * px; break;
+        case B200S_STATE_FINAL_T: src = im.final_T; bytes = 4 * px; break;
+        case B200S_STATE_POINT_LIST:
+        case B200S_STATE_POINT_LIST_KEYS: {
+            if (!a->bin_ws || num_rendered > a->bin_capacity) return B200S_E_BADARG;
+            BinWS bw = carve_bin(a->bin_ws, a->bin_capacity);
+            const int fb = sort_num_passes(d.tiles) & 1;
+            if (which == B200S_STATE_POINT_LIST) { src = bw.vals[fb]; bytes = 4 * num_rendered; }
+            else { src = bw.keys[fb]; bytes = 8 * num_rendered; }
+            break;
+        }
+        default: return B200S_E_BADARG;
+    }
+    if (bytes > dst_bytes) return B200S_E_WORKSPACE;
+    if (bytes == 0) return 0;
+    if (src) {
+        if (cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, stream) != cudaSuccess) return B200S_E_BADARG;
+    } else {
+        export_rec_kernel<<<(unsigned)((P + 255) / 256), 256, 0, stream>>>((int)P, g.rec, a->radii, g.clamped, which,
+                                                                         (float*)dst, (uint8_t*)dst);
+        if (cudaGetLastError() != cudaSuccess) return B200S_E_BADARG;
+    }
+    return bytes;
+}

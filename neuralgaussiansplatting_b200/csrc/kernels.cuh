@@ -1,0 +1,99 @@
+// Kernel parameter blocks and host launchers shared between the translation units.
+#pragma once
+#include "common.cuh"
+
+namespace b200s {
+
+struct PreprocessParams {
+    int P, D, M, W, H;
+    int grid_x, grid_y;
+    float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
+    int prefiltered;
+    const float* means3D;
+    const float* shs;
+    const float* colors_precomp;
+    const float* opacities;
+    const float* scales;
+    const float* rotations;
+    const float* cov3D_precomp;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* campos;
+    int* radii;
+    SplatRec* rec;
+    uint32_t* tiles_touched;
+    uint8_t* clamped;
+    B200sHeader* header;
+    uint32_t* counters;
+};
+
+struct BlendFwdParams {
+    int W, H, grid_x, grid_y;
+    const uint2* ranges;
+    const uint32_t* point_list;
+    const SplatRec* rec;
+    const float* background;
+    float* final_T;
+    uint32_t* n_contrib;
+    uint32_t* tile_last;
+    float* out_color;
+};
+
+struct BlendBwdParams {
+    int W, H, grid_x, grid_y;
+    const uint2* ranges;
+    const uint32_t* point_list;
+    const SplatRec* rec;
+    const uint32_t* point_offsets;   // deterministic mode: slot of an instance
+    const float* background;
+    const float* final_T;
+    const uint32_t* n_contrib;
+    const uint32_t* tile_last;
+    const float* dL_dpix;
+    float* accum;      // [P][ACC_STRIDE] atomic mode
+    float* partial;    // [R][ACC_STRIDE] deterministic mode
+    int deterministic;
+};
+
+struct PreprocessBwdParams {
+    int P, D, M, W, H;
+    float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
+    const float* means3D;
+    const float* shs;
+    const float* colors_precomp;
+    const float* scales;
+    const float* rotations;
+    const float* cov3D_precomp;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* campos;
+    const int* radii;
+    const SplatRec* rec;
+    const uint8_t* clamped;
+    const uint32_t* point_offsets;
+    const float* accum;       // [P][ACC_STRIDE] (atomic mode) or NULL
+    const float* partial;     // [R][ACC_STRIDE] (deterministic mode) or NULL
+    float* dL_dmeans3D;
+    float* dL_dmeans2D;
+    float* dL_dopacity;
+    float* dL_dsh;
+    float* dL_dscales;
+    float* dL_drotations;
+    float* dL_dcolors;
+    float* dL_dcov3D;
+    float* dL_dconic;
+};
+
+int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
+int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
+int launch_scan(const uint32_t* in, uint32_t* out, int P, uint32_t* status, uint32_t* counters,
+                B200sHeader* header, cudaStream_t stream);
+int sort_num_passes(int tiles);
+int launch_binning(int P, const SplatRec* rec, const uint32_t* offsets, const BinWS& bw, int64_t capacity,
+                   int64_t n_hint, int grid_x, int tiles, uint2* ranges, B200sHeader* header,
+                   uint32_t* counters, int* final_buf, bool debug, cudaStream_t stream);
+int launch_blend_fwd(const BlendFwdParams& p, int nw, cudaStream_t stream);
+int launch_blend_bwd(const BlendBwdParams& p, int nw, cudaStream_t stream);
+int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream);
+
+}  // namespace b200s
