@@ -318,7 +318,7 @@ def forward_with_state(*args, names=None):
     P, W, H = a.P, a.W, a.H
     T = ((W + 15) // 16) * ((H + 15) // 16)
     with torch.cuda.device(dev):
-        for name in (names or _STATE_DTYPES):
+        for name in (_STATE_DTYPES if names is None else names):
             dtype, shape = _STATE_DTYPES[name]
             t = torch.zeros(shape(P, num_rendered, T, W * H), dtype=dtype, device=dev)
             nbytes = t.numel() * t.element_size()

@@ -28,46 +28,47 @@ __device__ const float kSH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0
                                     0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
                                     -0.5900435899266435f};
 
-// SH basis evaluation shared by forward and backward (computeColorFromSH, forward.cu:20-71).
-// `sh` points at 3*M floats (coefficient-major, RGB interleaved).
+// SH basis evaluation (computeColorFromSH, forward.cu:20-71). `sh(k)` returns coefficient k (RGB).
+// The operation order — one FMA per coefficient, accumulated in coefficient order, with the
+// polynomial factors contracted exactly as below — mirrors the SASS of the reference
+// preprocessCUDA built for sm_100, so the RGB (and therefore the `clamped` flags that gate
+// the SH gradient) come out bit-identical.
 template <typename LoadF3>
 __device__ __forceinline__ float3 sh_to_rgb(int deg, float x, float y, float z, LoadF3 sh) {
-    float3 c0 = sh(0);
-    float3 res = make_float3(kSH_C0 * c0.x, kSH_C0 * c0.y, kSH_C0 * c0.z);
+    const float3 c0 = sh(0);
+    float3 res = make_float3(fmul(c0.x, kSH_C0), fmul(c0.y, kSH_C0), fmul(c0.z, kSH_C0));
+#define B200S_SH_ACC(b, k)                                                        \
+    {                                                                             \
+        const float3 s_ = sh(k);                                                  \
+        res.x = ffma((b), s_.x, res.x); res.y = ffma((b), s_.y, res.y); res.z = ffma((b), s_.z, res.z); \
+    }
     if (deg > 0) {
-        float3 s1 = sh(1), s2 = sh(2), s3 = sh(3);
-        res.x = res.x - kSH_C1 * y * s1.x + kSH_C1 * z * s2.x - kSH_C1 * x * s3.x;
-        res.y = res.y - kSH_C1 * y * s1.y + kSH_C1 * z * s2.y - kSH_C1 * x * s3.y;
-        res.z = res.z - kSH_C1 * y * s1.z + kSH_C1 * z * s2.z - kSH_C1 * x * s3.z;
+        const float t1 = fmul(y, kSH_C1), t2 = fmul(z, kSH_C1), t3 = fmul(x, kSH_C1);
+        B200S_SH_ACC(-t1, 1) B200S_SH_ACC(t2, 2) B200S_SH_ACC(-t3, 3)
         if (deg > 1) {
-            float xx = x * x, yy = y * y, zz = z * z;
-            float xy = x * y, yz = y * z, xz = x * z;
-            float b4 = kSH_C2[0] * xy, b5 = kSH_C2[1] * yz, b6 = kSH_C2[2] * (2.0f * zz - xx - yy);
-            float b7 = kSH_C2[3] * xz, b8 = kSH_C2[4] * (xx - yy);
-            float3 s4 = sh(4), s5 = sh(5), s6 = sh(6), s7 = sh(7), s8 = sh(8);
-            res.x = res.x + b4 * s4.x + b5 * s5.x + b6 * s6.x + b7 * s7.x + b8 * s8.x;
-            res.y = res.y + b4 * s4.y + b5 * s5.y + b6 * s6.y + b7 * s7.y + b8 * s8.y;
-            res.z = res.z + b4 * s4.z + b5 * s5.z + b6 * s6.z + b7 * s7.z + b8 * s8.z;
+            const float xx = fmul(x, x), yy = fmul(y, y), zz = fmul(z, z);
+            const float xy = fmul(y, x), yz = fmul(z, y), xz = fmul(z, x);
+            const float zz2 = fadd(zz, zz);
+            const float xx_yy = fsub(xx, yy);
+            B200S_SH_ACC(fmul(xy, kSH_C2[0]), 4)
+            B200S_SH_ACC(fmul(yz, kSH_C2[1]), 5)
+            B200S_SH_ACC(fmul(fsub(fsub(zz2, xx), yy), kSH_C2[2]), 6)
+            B200S_SH_ACC(fmul(xz, kSH_C2[3]), 7)
+            B200S_SH_ACC(fmul(xx_yy, kSH_C2[4]), 8)
             if (deg > 2) {
-                float b9 = kSH_C3[0] * y * (3.0f * xx - yy);
-                float b10 = kSH_C3[1] * xy * z;
-                float b11 = kSH_C3[2] * y * (4.0f * zz - xx - yy);
-                float b12 = kSH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy);
-                float b13 = kSH_C3[4] * x * (4.0f * zz - xx - yy);
-                float b14 = kSH_C3[5] * z * (xx - yy);
-                float b15 = kSH_C3[6] * x * (xx - 3.0f * yy);
-                float3 s9 = sh(9), s10 = sh(10), s11 = sh(11), s12 = sh(12), s13 = sh(13), s14 = sh(14),
-                       s15 = sh(15);
-                res.x = res.x + b9 * s9.x + b10 * s10.x + b11 * s11.x + b12 * s12.x + b13 * s13.x +
-                        b14 * s14.x + b15 * s15.x;
-                res.y = res.y + b9 * s9.y + b10 * s10.y + b11 * s11.y + b12 * s12.y + b13 * s13.y +
-                        b14 * s14.y + b15 * s15.y;
-                res.z = res.z + b9 * s9.z + b10 * s10.z + b11 * s11.z + b12 * s12.z + b13 * s13.z +
-                        b14 * s14.z + b15 * s15.z;
+                const float q = fsub(ffma(zz, 4.0f, -xx), yy);              // 4zz - xx - yy
+                B200S_SH_ACC(fmul(fmul(y, kSH_C3[0]), ffma(xx, 3.0f, -yy)), 9)
+                B200S_SH_ACC(fmul(fmul(xy, kSH_C3[1]), z), 10)
+                B200S_SH_ACC(fmul(fmul(y, kSH_C3[2]), q), 11)
+                B200S_SH_ACC(fmul(fmul(z, kSH_C3[3]), ffma(yy, -3.0f, ffma(xx, -3.0f, zz2))), 12)
+                B200S_SH_ACC(fmul(q, fmul(x, kSH_C3[4])), 13)
+                B200S_SH_ACC(fmul(xx_yy, fmul(z, kSH_C3[5])), 14)
+                B200S_SH_ACC(fmul(fmul(x, kSH_C3[6]), ffma(yy, -3.0f, xx)), 15)
             }
         }
     }
-    res.x += 0.5f; res.y += 0.5f; res.z += 0.5f;
+#undef B200S_SH_ACC
+    res.x = fadd(res.x, 0.5f); res.y = fadd(res.y, 0.5f); res.z = fadd(res.z, 0.5f);
     return res;
 }
 
@@ -155,9 +156,10 @@ preprocess_fwd_kernel(const __grid_constant__ PreprocessParams p) {
     } else {
         float dx = 0.f, dy = 0.f, dz = 0.f;
         if (visible) {
-            dx = px - p.campos[0]; dy = py - p.campos[1]; dz = pz - p.campos[2];
-            const float len = sqrtf(dx * dx + dy * dy + dz * dz);
-            dx = dx / len; dy = dy / len; dz = dz / len;
+            // glm::length as compiled: sqrt(fma(dz,dz, fma(dx,dx, dy*dy))), then IEEE divisions
+            dx = fsub(px, p.campos[0]); dy = fsub(py, p.campos[1]); dz = fsub(pz, p.campos[2]);
+            const float len = __fsqrt_rn(ffma(dz, dz, ffma(dx, dx, fmul(dy, dy))));
+            dx = __fdiv_rn(dx, len); dy = __fdiv_rn(dy, len); dz = __fdiv_rn(dz, len);
         }
         float3 res;
         if (SH16) {

@@ -36,14 +36,14 @@ class SceneConfig:
         return 2.0 * math.atan(math.tan(self.fovx * 0.5) * self.height / self.width)
 
 
-# log_scale_mu values come from tools in tests/golden/calibrate_scales.py (bisection on the CPU
-# oracle's tiles_touched at camera 0); the achieved N / P_vis is recorded in DESIGN.md.
+# log_scale_mu values come from tools/calibrate_scales.py (bisection on the CPU oracle's tiles_touched at
+# camera 0 so that num_rendered / visible Gaussians = 6.0); achieved values are in DESIGN.md.
 CONFIGS: Dict[str, SceneConfig] = {
-    "C1": SceneConfig("C1", 50_000, 800, 800, 0.6911112, "nerf", 4.031, 0.0, -3.70),
-    "C2": SceneConfig("C2", 300_000, 800, 800, 0.6911112, "nerf", 4.031, 0.0, -3.70),
-    "C3": SceneConfig("C3", 3_000_000, 1344, 896, 1.0, "360", 4.0, 1.0, -3.95),
-    "C4": SceneConfig("C4", 6_000_000, 1920, 1080, 1.2, "360", 4.0, 1.0, -4.10, views=64),
-    "C5": SceneConfig("C5", 3_000_000, 1344, 896, 1.0, "360", 4.0, 1.0, -3.95, views=8),
+    "C1": SceneConfig("C1", 50_000, 800, 800, 0.6911112, "nerf", 4.031, 0.0, -4.86),
+    "C2": SceneConfig("C2", 300_000, 800, 800, 0.6911112, "nerf", 4.031, 0.0, -4.86),
+    "C3": SceneConfig("C3", 3_000_000, 1344, 896, 1.0, "360", 4.0, 1.0, -4.91),
+    "C4": SceneConfig("C4", 6_000_000, 1920, 1080, 1.2, "360", 4.0, 1.0, -5.07, views=64),
+    "C5": SceneConfig("C5", 3_000_000, 1344, 896, 1.0, "360", 4.0, 1.0, -4.91, views=8),
     # tiny shapes for tests
     "T0": SceneConfig("T0", 2_000, 160, 96, 0.9, "nerf", 4.031, 0.5, -2.6),
     "T1": SceneConfig("T1", 20_000, 400, 304, 0.8, "360", 4.0, 1.0, -2.9),

@@ -1,0 +1,98 @@
+"""world_size-2 gloo tests of the view-parallel plumbing (parallel.py): view sharding, the bucketed gradient
+all-reduce, replica consistency, densification-statistics reduction."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from neuralgaussiansplatting_b200 import parallel as par
+
+
+def test_shard_views_round_robin():
+    assert par.shard_views(8, 0, 8) == [0] and par.shard_views(8, 7, 8) == [7]
+    assert par.shard_views(64, 3, 8) == list(range(3, 64, 8))
+    assert par.shard_views(3, 3, 4) == []
+    got = sorted(v for r in range(4) for v in par.shard_views(10, r, 4))
+    assert got == list(range(10))
+    assert all(par.owner_of_view(v, 4) == r for r in range(4) for v in par.shard_views(10, r, 4))
+    with pytest.raises(ValueError):
+        par.shard_views(8, 8, 8)
+
+
+def test_payload_matches_survey_figure():
+    assert par.allreduce_payload_bytes(3_000_000) == 708_000_000      # 236 B/Gaussian
+    assert par.GRAD_FLOATS_PER_GAUSSIAN * 4 == 236
+
+
+def test_buckets_cover_every_element_once():
+    P = 1000
+    g = dict(means3D=torch.zeros(P, 3), shs=torch.zeros(P, 16, 3), opacities=torch.zeros(P, 1),
+             scales=torch.zeros(P, 3), rotations=torch.zeros(P, 4))
+    ar = par.GradientAllReduce(max_bucket_bytes=40_000)
+    bks = ar.buckets(g)
+    assert sum(b.numel() for b in bks) == P * 59
+    assert max(b.numel() * 4 for b in bks) <= 40_000 + 16 * 3 * 4 * 8
+    for b in bks:
+        b += 1.0
+    assert all(float(v.min()) == 1.0 and float(v.max()) == 1.0 for v in g.values())   # views, not copies
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        P = 257
+        torch.manual_seed(0)                      # identical replicas
+        params = dict(means3D=torch.randn(P, 3), shs=torch.randn(P, 16, 3), opacities=torch.randn(P, 1),
+                      scales=torch.randn(P, 3), rotations=torch.randn(P, 4))
+        assert par.replicas_in_sync(params.values())
+        # each rank "renders" its own views: deterministic per-view gradients, accumulated locally
+        views = par.shard_views(5, rank, world)
+        total = {}
+        for v in views:
+            gen = torch.Generator().manual_seed(100 + v)
+            part = {k: torch.randn(p.shape, generator=gen) for k, p in params.items()}
+            par.accumulate_(total, part)
+        ar = par.GradientAllReduce(max_bucket_bytes=20_000)
+        ar.start(total)
+        ar.wait()
+        # expected: sum over all 5 views
+        exp = {}
+        for v in range(5):
+            gen = torch.Generator().manual_seed(100 + v)
+            par.accumulate_(exp, {k: torch.randn(p.shape, generator=gen) for k, p in params.items()})
+        ok = all(torch.allclose(total[k], exp[k], atol=1e-5) for k in params)
+        for k in params:                          # identical SGD step on every rank
+            params[k] -= 0.01 * total[k]
+        ok = ok and par.replicas_in_sync(params.values())
+        st = par.DensificationStats(P, "cpu")
+        vis = torch.zeros(P, dtype=torch.bool); vis[rank::world] = True
+        st.add_view(torch.ones(P, 3), vis)
+        st.allreduce()
+        ok = ok and float(st.denom.sum()) == P and abs(float(st.accum.sum()) - P * 2 ** 0.5) < 1e-3
+        params["means3D"][0, 0] += float(rank)    # deliberately diverge -> must be detected
+        ok = ok and not par.replicas_in_sync(params.values())
+        q.put((rank, ok))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gradient_allreduce_world2_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert sorted(res) == [(0, True), (1, True)]
