@@ -1,0 +1,492 @@
+"""bench.py — the rasterizer hot path on B200, one JSON line (driver contract).
+
+    python bench.py --gpus N --steps K --warmup W                 # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K --warmup W  # the unmodified reference (oracle/_ref)
+
+Workload (config.workload): BASELINE.json's metric configuration that fits one GPU — C3, the
+Mip-NeRF360-shaped training step: 3 M Gaussians, SH degree 3, 1344x896, forward + backward of ONE view per
+step per GPU (synthetic seeded Gaussians / cameras). With N > 1 each rank rasterizes its own
+view (weak scaling over views) and the 59-float per-Gaussian gradients are SUM-all-reduced over NCCL.
+
+  value            train-step views/s over all ranks, inputs resident in HBM (device-timed, max over ranks)
+  e2e              the same step through the drop-in Python API (GaussianRasterizer + autograd), with the
+                   per-step host inputs (camera matrices + ground-truth image, pinned) copied H2D and the loss
+                   read back D2H inside the timed region — what train.py:86-93 does per iteration
+  roofline         the dominant kernel of the step: algorithmic flops (or bytes) / its CUDA-event time, measured
+                   live with the library's stage brackets in a separate pass of the same K steps
+  cpu_baseline     torch-CPU preprocessing the north_star names (covariance + eval_sh) and the C oracle of the
+                   full step, on a bounded sample, on this box's host cores
+The reference arm runs the UNMODIFIED reference rasterizer compiled for sm_100 (oracle/_ref, the same-GPU
+baseline the north_star's ">= 2x" is quoted against); the reference has no CPU implementation of this path.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+METRIC = "train-step views/s (rasterizer fwd+bwd) at 3M Gaussians, SH3, 1344x896"
+UNIT = "views/s"
+
+
+# ----------------------------------------------------------------------------------------- utilities
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (profiling recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.splitlines()[0].split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def env_world():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def barrier_sync(world, dev):
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+
+
+def timed_region(fn, steps, world, dev, sampler=None):
+    """EXACTLY `steps` calls of fn(step) between barrier+synchronize, CUDA events on the current stream,
+    MAX over ranks."""
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier_sync(world, dev)
+    e0.record()
+    for s in range(steps):
+        fn(s)
+    e1.record()
+    barrier_sync(world, dev)
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def load_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
+
+
+# ----------------------------------------------------------------------------------------- workload
+class Workload:
+    """C3: 3 M replicated Gaussians, 8 orbit views, per-view dL/dimage and ground-truth images."""
+
+    def __init__(self, name, dev, rank, world, pin_host=True):
+        from neuralgaussiansplatting_b200.synthetic import CONFIGS, make_camera, make_grad_image, make_scene
+        self.cfg = cfg = CONFIGS[name]
+        self.dev, self.rank, self.world = dev, rank, world
+        self.nviews = max(cfg.views, 8)
+        sc = make_scene(cfg, seed=0)
+        self.scene = {k: v.to(dev) for k, v in sc.items() if k not in ("feature_vector", "normal")}
+        self.P = self.scene["means3D"].shape[0]
+        self.bg = torch.zeros(3, device=dev)
+        self.cams_host = [make_camera(cfg, v) for v in range(self.nviews)]
+        self.cams = [make_camera(cfg, v, device=dev) for v in range(self.nviews)]
+        self.tan = (math.tan(cfg.fovx * 0.5), math.tan(cfg.fovy * 0.5))
+        self.dL = [make_grad_image(cfg, v, device=dev) for v in range(self.nviews)]
+        # host-side per-step inputs of the e2e leg: camera block [16 + 16 + 3 floats] and ground truth image
+        g = torch.Generator().manual_seed(4000)
+        self.gt_host = [torch.rand(3, cfg.height, cfg.width, generator=g) for _ in range(self.nviews)]
+        self.cam_host = [torch.cat([c.world_view_transform.reshape(-1), c.full_proj_transform.reshape(-1),
+                                    c.camera_center.reshape(-1)]) for c in self.cams_host]
+        if pin_host:
+            self.gt_host = [t.pin_memory() for t in self.gt_host]
+            self.cam_host = [t.pin_memory() for t in self.cam_host]
+        self.h2d_bytes = self.gt_host[0].numel() * 4 + self.cam_host[0].numel() * 4
+        self.d2h_bytes = 4
+
+    def view_of(self, step):
+        return (step * self.world + self.rank) % self.nviews
+
+    def fwd_args(self, v):
+        s, c = self.scene, self.cams[v]
+        E = torch.Tensor([])
+        return (self.bg, s["means3D"], E, s["opacities"], s["scales"], s["rotations"], 1.0, E,
+                c.world_view_transform, c.full_proj_transform, self.tan[0], self.tan[1], self.cfg.height,
+                self.cfg.width, s["shs"], 3, c.camera_center, False, False)
+
+
+def stage_table(w: Workload, stage_ms, stage_calls, steps, counts, P_vis, N, hbm_peak, fp32_peak):
+    """Per-stage achieved rate against its roofline. Algorithmic bytes/flops: SURVEY.md §8(d) / DESIGN.md."""
+    from neuralgaussiansplatting_b200 import _lib
+    P, px = w.P, w.cfg.width * w.cfg.height
+    T = ((w.cfg.width + 15) // 16) * ((w.cfg.height + 15) // 16)
+    P_c = P - P_vis
+    passes = -(-(32 + max(T - 1, 1).bit_length()) // 8)
+    n_trav, n_contrib, n_trav_bwd = counts
+    alg = {
+        "preprocess": ("hbm", 311 * P_vis + 20 * P_c),
+        "scan": ("hbm", 8 * P),
+        "expand": ("hbm", 20 * P + 12 * N),
+        "sort": ("hbm", N * (8 + 24 * passes)),
+        "ranges": ("hbm", 8 * N + 8 * T),
+        "blend_fwd": ("fp32", 14 * n_trav + 9 * n_contrib),
+        "blend_bwd": ("fp32", 14 * n_trav_bwd + 69 * n_contrib),
+        "preprocess_bwd": ("hbm", 510 * P_vis + 4 * P_c + 236 * P_c),
+    }
+    rows = {}
+    for i, name in enumerate(_lib.STAGES):
+        if stage_calls[i] == 0:
+            continue
+        ms = stage_ms[i] / steps
+        row = {"ms_per_step": round(ms, 5), "launch_brackets_per_step": stage_calls[i] / steps}
+        if name in alg and ms > 0:
+            bound, units = alg[name]
+            if bound == "hbm":
+                ach = units / (ms * 1e-3) / 1e9
+                row.update(bound="hbm", algorithmic_bytes=int(units), achieved=round(ach, 1), peak=hbm_peak,
+                           unit="GB/s", frac=round(ach / hbm_peak, 4))
+            else:
+                ach = units / (ms * 1e-3) / 1e12
+                row.update(bound="fp32", algorithmic_flops=int(units), achieved=round(ach, 3),
+                           peak=round(fp32_peak, 2), unit="TFLOP/s", frac=round(ach / fp32_peak, 4))
+        rows[name] = row
+    return rows
+
+
+# ----------------------------------------------------------------------------------------- our arm
+def run_ours(args, rank, local_rank, world, dev):
+    import ctypes as C
+    from neuralgaussiansplatting_b200 import _C, _lib, parallel
+    from neuralgaussiansplatting_b200.diff_gaussian_rasterization import (GaussianRasterizationSettings,
+                                                                          GaussianRasterizer)
+    lib = _lib.load()          # raises if libb200splat.so is missing: there is no fallback path
+    w = Workload(args.workload, dev, rank, world)
+    cfg = w.cfg
+    reducer = parallel.GradientAllReduce() if world > 1 else None
+    GRAD_KEYS = {"means3D": 3, "opacities": 2, "shs": 5, "scales": 6, "rotations": 7}   # slots of the 8-tuple
+
+    def step_resident(s):
+        v = w.view_of(s)
+        fa = w.fwd_args(v)
+        out = _C.rasterize_gaussians(*fa)
+        g = _C.rasterize_gaussians_backward(fa[0], fa[1], out[2], fa[2], fa[4], fa[5], fa[6], fa[7], fa[8], fa[9],
+                                            fa[10], fa[11], w.dL[v], fa[14], fa[15], fa[16], out[3], out[0], out[4],
+                                            out[5], False)
+        if reducer is not None:
+            reducer.start({k: g[i] for k, i in GRAD_KEYS.items()})
+            reducer.wait()
+        return g
+
+    # ---- e2e: the call a user makes (nn.Module + autograd), host inputs copied inside the timed region
+    params = {k: w.scene[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "scales", "rotations", "shs")}
+    cam_dev = torch.empty(35, device=dev)
+    gt_dev = torch.empty(3, cfg.height, cfg.width, device=dev)
+    loss_host = torch.zeros(1).pin_memory()
+
+    def step_e2e(s):
+        v = w.view_of(s)
+        cam_dev.copy_(w.cam_host[v], non_blocking=True)
+        gt_dev.copy_(w.gt_host[v], non_blocking=True)
+        settings = GaussianRasterizationSettings(cfg.height, cfg.width, w.tan[0], w.tan[1], w.bg, 1.0,
+                                                 cam_dev[0:16].view(4, 4), cam_dev[16:32].view(4, 4), 3,
+                                                 cam_dev[32:35], False, False)
+        m2d = torch.zeros_like(params["means3D"], requires_grad=True)
+        img, radii = GaussianRasterizer(settings)(means3D=params["means3D"], means2D=m2d, shs=params["shs"],
+                                                  colors_precomp=None, opacities=params["opacities"],
+                                                  scales=params["scales"], rotations=params["rotations"],
+                                                  cov3D_precomp=None)
+        loss = (img - gt_dev).abs().mean()
+        loss.backward()
+        if reducer is not None:
+            reducer.start({k: p.grad for k, p in params.items()})
+            reducer.wait()
+        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()       # the step's result is on the host
+        for p in params.values():
+            p.grad = None
+
+    for s in range(args.warmup):
+        step_resident(s)
+    launches0 = lib.b200s_launch_count()
+    with ClockSampler(local_rank) as clk:
+        ms_total = timed_region(step_resident, args.steps, world, dev)
+    launches = int(lib.b200s_launch_count() - launches0)
+    for s in range(max(args.warmup, 3)):
+        step_e2e(s)
+    ms_e2e = timed_region(step_e2e, args.steps, world, dev)
+
+    out = {
+        "metric": METRIC, "value": round(world * args.steps / (ms_total * 1e-3), 3), "unit": UNIT,
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(ms_total / args.steps, 4), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{cfg.name}: {w.P} Gaussians SH3, {cfg.width}x{cfg.height}, fwd+bwd, 1 view/step/GPU "
+                               f"cycling {w.nviews} orbit views" + (", + NCCL SUM all-reduce of 59 floats/Gaussian"
+                                                                     if world > 1 else ""),
+                   "parallelism": f"view-parallel x{world}, Gaussians replicated",
+                   "l2": "inputs (708 MB of Gaussian parameters) exceed the 126 MB L2; no explicit flush",
+                   "blend_mode": "strict (expf, bit-exact n_contrib)"},
+        "e2e": {"value": round(world * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
+                "ms_per_step": round(ms_e2e / args.steps, 4), "h2d_bytes_per_step": w.h2d_bytes,
+                "d2h_bytes_per_step": w.d2h_bytes,
+                "api": "GaussianRasterizer(nn.Module)+autograd, L1 loss vs host ground truth"},
+        "gpu_launches": launches,
+        "clocks": clk.summary(),
+    }
+    if rank == 0:
+        out.update(roofline_pass(args, w, lib, _C, step_resident))
+        if not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(w)
+    return out
+
+
+def roofline_pass(args, w, lib, _C, step_fn):
+    """Separate pass of K steps on view_of(0) with the library's per-stage CUDA-event brackets enabled."""
+    import ctypes as C
+    from neuralgaussiansplatting_b200 import _lib
+    dev = w.dev
+    hbm_peak, peak_src, sm_max = load_peaks()
+    fp32_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12
+    v = w.view_of(0)
+    saved = w.view_of
+    w.view_of = lambda s: v
+    try:
+        for s in range(2):
+            step_fn(s)
+        torch.cuda.synchronize(dev)
+        lib.b200s_profile_begin()
+        for s in range(args.steps):
+            step_fn(s)
+        ms = (C.c_float * len(_lib.STAGES))()
+        calls = (C.c_int32 * len(_lib.STAGES))()
+        _lib.check(lib.b200s_profile_end(ms, calls), "b200s_profile_end")
+    finally:
+        w.view_of = saved
+    # exact pair counts and visibility of that view
+    outp, a, keep = _C._forward_impl(*w.fwd_args(v))
+    counts_dev = torch.zeros(3, dtype=torch.int64, device=dev)
+    _lib.check(lib.b200s_count_pairs(C.byref(a), counts_dev.data_ptr(), torch.cuda.current_stream().cuda_stream),
+               "b200s_count_pairs")
+    counts = [int(x) for x in counts_dev.cpu()]
+    P_vis, N = int((outp[2] > 0).sum()), int(outp[0])
+    rows = stage_table(w, list(ms), list(calls), args.steps, counts, P_vis, N, hbm_peak, fp32_peak)
+    top = max((k for k in rows if "frac" in rows[k]), key=lambda k: rows[k]["ms_per_step"])
+    r = rows[top]
+    roof = {"kernel": top, "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
+            "frac": r["frac"], "traffic": None, "ms_per_launch": r["ms_per_step"],
+            "peak_source": (peak_src if r["bound"] == "hbm" else
+                            f"nominal FP32 FMA: 148 SM x 128 lanes x 2 x {sm_max:.0f} MHz (no measured FP32 peak)"),
+            "share_of_step": round(r["ms_per_step"] / sum(x["ms_per_step"] for x in rows.values()), 4)}
+    return {"roofline": roof, "stages": rows,
+            "workload_counts": {"P": w.P, "P_visible": P_vis, "num_rendered": N, "pairs_traversed_fwd": counts[0],
+                                "pairs_contributing": counts[1], "pairs_traversed_bwd": counts[2]}}
+
+
+# ----------------------------------------------------------------------------------------- CPU baseline
+def cpu_baseline(w: Workload):
+    """Reported baseline, not the target. (1) The CPU column the north_star names: the reference's torch-side
+    preprocessing (build_covariance_from_scaling_rotation + eval_sh + clamp, gaussian_renderer/__init__.py:63-81)
+    on all P Gaussians on the host cores; (2) the C oracle (oracle/oracle_cpu.c, the one place bench.py executes
+    oracle/) for one full forward+backward view of the same workload, OpenMP on all cores."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    from neuralgaussiansplatting_b200.sh_utils import build_covariance_from_scaling_rotation, eval_sh
+    cores = os.cpu_count() or 1
+    sc = {k: v.cpu() for k, v in w.scene.items()}
+    cam = w.cams_host[0]
+
+    def torch_pre():
+        cov = build_covariance_from_scaling_rotation(sc["scales"], 1.0, sc["rotations"])
+        d = sc["means3D"] - cam.camera_center[None, :]
+        d = d / d.norm(dim=1, keepdim=True)
+        col = torch.clamp_min(eval_sh(3, sc["shs"].transpose(1, 2), d) + 0.5, 0.0)
+        return cov, col
+
+    res = {}
+    for nthreads in (1, cores):
+        torch.set_num_threads(nthreads)
+        torch_pre()
+        best = min(_timeit(torch_pre) for _ in range(3))
+        res[f"torch_cpu_preprocess_ms_{nthreads}t"] = round(best * 1e3, 2)
+    out = {"unit": UNIT, "cores": cores, "kind": "port",
+           "torch_cpu_preprocess": dict(res, P=w.P, what="covariance + eval_sh(deg 3) + clamp, fp32")}
+    try:
+        import oracle_cpu
+        oracle_cpu.set_threads(cores)
+        t0 = time.perf_counter()
+        o = oracle_cpu.render_scene(w.cfg, sc, cam, w.bg.cpu(), dL_dpix=w.dL[0].cpu(), as_torch=False)
+        dt = time.perf_counter() - t0
+        out.update(value=round(1.0 / dt, 5), sample=f"1 view of {w.cfg.name} forward+backward through the C oracle "
+                   f"({dt:.1f} s, {oracle_cpu.max_threads()} OpenMP threads; binning serial)",
+                   oracle_num_rendered=int(o["num_rendered"]))
+    except Exception as e:  # the oracle is test infrastructure; its absence must not hide the GPU numbers
+        out.update(value=None, sample=f"C oracle unavailable: {e}")
+    return out
+
+
+def _timeit(fn):
+    t0 = time.perf_counter()
+    fn()
+    return time.perf_counter() - t0
+
+
+# ----------------------------------------------------------------------------------------- reference arm
+def run_reference(args, rank, local_rank, world, dev):
+    """The UNMODIFIED reference rasterizer (diff-gaussian-rasterization, compiled for sm_100 into oracle/_ref by
+    oracle/build_ref.sh) on the same workload, metric and timing rules. Its torch binding's allocations
+    (torch::full / nine torch::zeros, rasterize_points.cu:68-69,151-159) are reproduced by tests/refbind.py."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import refbind
+    from neuralgaussiansplatting_b200 import parallel
+    if not refbind.available("ref_dgr"):
+        return {"impl": "reference", "unavailable": "oracle/_ref/libref_dgr.so was not built (needs /root/reference)"}
+    w = Workload(args.workload, dev, rank, world)
+    cfg = w.cfg
+    ref = refbind.RefDGR()
+    reducer = parallel.GradientAllReduce() if world > 1 else None
+    s_ = w.scene
+
+    def kw_of(v, view=None, proj=None, campos=None):
+        c = w.cams[v]
+        return dict(bg=w.bg, means3D=s_["means3D"], opacities=s_["opacities"],
+                    viewmatrix=c.world_view_transform if view is None else view,
+                    projmatrix=c.full_proj_transform if proj is None else proj,
+                    campos=c.camera_center if campos is None else campos, tan_fovx=w.tan[0], tan_fovy=w.tan[1],
+                    W=cfg.width, H=cfg.height, shs=s_["shs"], scales=s_["scales"], rotations=s_["rotations"])
+
+    BK = ("bg", "means3D", "viewmatrix", "projmatrix", "campos", "tan_fovx", "tan_fovy", "shs", "scales", "rotations")
+
+    def fwd_bwd(kw, dL):
+        R, color, radii = ref.forward(sync=False, **kw)
+        g = ref.backward(radii=radii, dL_dpix=dL, sync=False, **{k: kw[k] for k in BK})
+        if reducer is not None:
+            reducer.start({"means3D": g["means3D"], "opacities": g["opacity"], "shs": g["sh"], "scales": g["scales"],
+                           "rotations": g["rotations"]})
+            reducer.wait()
+        return color
+
+    def step_resident(s):
+        v = w.view_of(s)
+        fwd_bwd(kw_of(v), w.dL[v])
+
+    cam_dev = torch.empty(35, device=dev)
+    gt_dev = torch.empty(3, cfg.height, cfg.width, device=dev)
+    loss_host = torch.zeros(1).pin_memory()
+
+    def step_e2e(s):
+        v = w.view_of(s)
+        cam_dev.copy_(w.cam_host[v], non_blocking=True)
+        gt_dev.copy_(w.gt_host[v], non_blocking=True)
+        kw = kw_of(v, cam_dev[0:16].view(4, 4), cam_dev[16:32].view(4, 4), cam_dev[32:35])
+        R, color, radii = ref.forward(sync=False, **kw)
+        diff = color - gt_dev
+        loss = diff.abs().mean()
+        dL = torch.sign(diff) / diff.numel()                 # d(L1 mean)/d(color), what autograd would hand back
+        g = ref.backward(radii=radii, dL_dpix=dL, sync=False, **{k: kw[k] for k in BK})
+        if reducer is not None:
+            reducer.start({"means3D": g["means3D"], "opacities": g["opacity"], "shs": g["sh"], "scales": g["scales"],
+                           "rotations": g["rotations"]})
+            reducer.wait()
+        loss_host.copy_(loss.reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for s in range(args.warmup):
+        step_resident(s)
+    with ClockSampler(local_rank) as clk:
+        ms_total = timed_region(step_resident, args.steps, world, dev)
+    for s in range(max(args.warmup, 3)):
+        step_e2e(s)
+    ms_e2e = timed_region(step_e2e, args.steps, world, dev)
+    ref.close()
+    value = round(world * args.steps / (ms_total * 1e-3), 3)
+    return {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(ms_total / args.steps, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{cfg.name}: {w.P} Gaussians SH3, {cfg.width}x{cfg.height}, fwd+bwd, 1 view/step/GPU "
+                               f"cycling {w.nviews} orbit views" + (", + NCCL SUM all-reduce of 59 floats/Gaussian"
+                                                                     if world > 1 else ""),
+                   "parallelism": f"view-parallel x{world}, Gaussians replicated",
+                   "what": "unmodified reference diff-gaussian-rasterization kernels compiled for sm_100 "
+                           "(oracle/_ref), same GPU, same inputs; the reference has no CPU implementation of this "
+                           "path and no multi-GPU code (the all-reduce at N>1 is this repo's NCCL plumbing)"},
+        "e2e": {"value": round(world * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
+                "ms_per_step": round(ms_e2e / args.steps, 4), "h2d_bytes_per_step": w.h2d_bytes,
+                "d2h_bytes_per_step": w.d2h_bytes},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
+                         "sample": "GPU run of the reference kernels (CUDA-only reference: no host-core path exists); "
+                                   f"{args.steps} full steps"},
+        "clocks": clk.summary(),
+    }
+
+
+# ----------------------------------------------------------------------------------------- main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C3")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank, local_rank, world = env_world()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the rasterizer has no CPU path")
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        raise SystemExit(f"--gpus {args.gpus} needs torchrun (WORLD_SIZE={world})")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    try:
+        res = run_reference(args, rank, local_rank, world, dev) if args.impl == "reference" else \
+            run_ours(args, rank, local_rank, world, dev)
+        if rank == 0:
+            print(json.dumps(res), flush=True)
+    finally:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -216,6 +216,36 @@ enum {
 int64_t b200s_export_state(const B200sForwardArgs* args, int32_t which, int64_t num_rendered,
                            void* dst, int64_t dst_bytes, b200s_stream_t stream);
 
+/* ---- measurement hooks (bench.py / tests only; never needed for results).
+ * Stage timing: between b200s_profile_begin() and b200s_profile_end() every stage of every
+ * forward / backward call is bracketed by cudaEvents on the caller's stream (no
+ * synchronisation until _end, which waits for the last event and sums per stage).
+ * b200s_launch_count() is the cumulative number of kernels this library has launched. */
+enum {
+    B200S_STAGE_PREPROCESS = 0,    /* fused preprocess forward (K1) */
+    B200S_STAGE_SCAN = 1,          /* prefix sum of tiles_touched (K2) */
+    B200S_STAGE_EXPAND = 2,        /* duplicateWithKeys (K3) */
+    B200S_STAGE_SORT = 3,          /* histogram + onesweep passes (K4) */
+    B200S_STAGE_RANGES = 4,        /* identifyTileRanges (K5) */
+    B200S_STAGE_BLEND_FWD = 5,     /* forward compositing (K6) */
+    B200S_STAGE_BLEND_BWD = 6,     /* backward compositing (K7) */
+    B200S_STAGE_PREPROCESS_BWD = 7,/* fused preprocess backward (K8+K9) */
+    B200S_STAGE_IDXMAP = 8,        /* idxmap forward (K11..K15) */
+    B200S_STAGE_IDXMAP_BWD = 9,    /* idxmap backward (K16) */
+    B200S_STAGE_MISC = 10,         /* memsets and small bookkeeping kernels */
+    B200S_NUM_STAGES = 11
+};
+int b200s_profile_begin(void);
+/* ms[B200S_NUM_STAGES] (summed elapsed time) and calls[B200S_NUM_STAGES] (brackets recorded). */
+int b200s_profile_end(float* ms, int32_t* calls);
+uint64_t b200s_launch_count(void);
+
+/* Roofline accounting: replays the per-pixel traversal of the last forward and counts
+ * counts_dev[0] = (pixel, Gaussian) pairs the forward traverses (reference `contributor` at
+ * exit, forward.cu:325-351), [1] = pairs that contribute, [2] = pairs the backward traverses
+ * (sum of n_contrib). counts_dev: device u64[3]. */
+int b200s_count_pairs(const B200sForwardArgs* args, unsigned long long* counts_dev, b200s_stream_t stream);
+
 /* sizeof() of the ABI structs as compiled: 0 B200sHeader, 1 B200sForwardArgs,
  * 2 B200sBackwardArgs, 3 B200sIdxmapArgs. Bindings assert their own layout against it. */
 size_t b200s_sizeof(int32_t which);

@@ -82,6 +82,9 @@ STATE = {
     "point_list": 6, "point_list_keys": 7, "ranges": 8, "n_contrib": 9, "final_T": 10, "clamped": 11,
 }
 
+STAGES = ("preprocess", "scan", "expand", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "idxmap",
+          "idxmap_bwd", "misc")
+
 ERRORS = {
     -1: "B200S_E_BADARG (NULL or inconsistent arguments)",
     -2: "B200S_E_WORKSPACE (workspace smaller than required)",
@@ -109,6 +112,10 @@ SYMBOLS = [
     ("b200s_idxmap_workspace_size", C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     ("b200s_idxmap_forward", C.c_int, [C.POINTER(IdxmapArgs), C.c_void_p]),
     ("b200s_idxmap_backward", C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ("b200s_profile_begin", C.c_int, []),
+    ("b200s_profile_end", C.c_int, [C.c_void_p, C.c_void_p]),
+    ("b200s_launch_count", C.c_uint64, []),
+    ("b200s_count_pairs", C.c_int, [C.POINTER(ForwardArgs), C.c_void_p, C.c_void_p]),
     ("b200s_export_state", C.c_int64, [C.POINTER(ForwardArgs), C.c_int32, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
 ]
 

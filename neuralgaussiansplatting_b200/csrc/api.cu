@@ -3,8 +3,11 @@
 // caller's stream. Replaces CudaRasterizer::Rasterizer::{forward,backward,markVisible}
 // (reference rasterizer_impl.cu:141-153,198-434).
 
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <vector>
 #include "kernels.cuh"
 
 using namespace b200s;
@@ -15,6 +18,62 @@ int idxmap_backward_impl(int P, int W, int H, const int32_t* out_idx, const floa
                          float* dL_dfeature_vector, cudaStream_t stream);
 size_t idxmap_workspace_size_impl(int P, int W, int H);
 }
+
+// ------------------------------------------------------------------ measurement hooks
+namespace b200s {
+struct Bracket { int stage; cudaEvent_t e0, e1; };
+static std::atomic<bool> g_prof_on{false};
+static std::atomic<uint64_t> g_launches{0};
+static std::mutex g_prof_mu;
+static std::vector<Bracket> g_brackets;
+static std::vector<cudaEvent_t> g_open[B200S_NUM_STAGES];
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+void prof_begin(int stage, cudaStream_t stream) {
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, stream);
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    g_open[stage].push_back(e);
+}
+void prof_end(int stage, cudaStream_t stream) {
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (g_open[stage].empty()) return;
+    cudaEvent_t e0 = g_open[stage].back();
+    g_open[stage].pop_back();
+    cudaEvent_t e1;
+    if (cudaEventCreate(&e1) != cudaSuccess) { cudaEventDestroy(e0); return; }
+    cudaEventRecord(e1, stream);
+    g_brackets.push_back({stage, e0, e1});
+}
+}  // namespace b200s
+
+extern "C" int b200s_profile_begin(void) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    for (auto& b : g_brackets) { cudaEventDestroy(b.e0); cudaEventDestroy(b.e1); }
+    g_brackets.clear();
+    g_prof_on.store(true);
+    return 0;
+}
+extern "C" int b200s_profile_end(float* ms, int32_t* calls) {
+    g_prof_on.store(false);
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    for (int i = 0; i < B200S_NUM_STAGES; ++i) { if (ms) ms[i] = 0.f; if (calls) calls[i] = 0; }
+    int rc = 0;
+    for (auto& b : g_brackets) {
+        float t = 0.f;
+        cudaError_t e = cudaEventSynchronize(b.e1);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&t, b.e0, b.e1);
+        if (e != cudaSuccess) rc = (int)e;
+        else { if (ms) ms[b.stage] += t; if (calls) calls[b.stage] += 1; }
+        cudaEventDestroy(b.e0); cudaEventDestroy(b.e1);
+    }
+    g_brackets.clear();
+    for (auto& v : g_open) { for (auto e : v) cudaEventDestroy(e); v.clear(); }
+    return rc;
+}
+extern "C" uint64_t b200s_launch_count(void) { return g_launches.load(); }
 
 namespace {
 
@@ -125,10 +184,16 @@ int b200s_forward_preprocess(const B200sForwardArgs* a, b200s_stream_t stream_) 
     p.viewmatrix = a->viewmatrix; p.projmatrix = a->projmatrix; p.campos = a->campos;
     p.radii = a->radii; p.rec = g.rec; p.tiles_touched = g.tiles_touched; p.clamped = g.clamped;
     p.header = g.header; p.counters = g.counters;
-    rc = launch_preprocess_fwd(p, stream);
+    {
+        ProfScope ps(B200S_STAGE_PREPROCESS, stream);
+        rc = launch_preprocess_fwd(p, stream);
+    }
     if (rc) return rc;
     B200S_AFTER_LAUNCH(stream, a->debug);
-    rc = launch_scan(g.tiles_touched, g.point_offsets, a->P, g.scan_status, g.counters, g.header, stream);
+    {
+        ProfScope ps(B200S_STAGE_SCAN, stream);
+        rc = launch_scan(g.tiles_touched, g.point_offsets, a->P, g.scan_status, g.counters, g.header, stream);
+    }
     if (rc) return rc;
     B200S_AFTER_LAUNCH(stream, a->debug);
     return 0;
@@ -164,7 +229,10 @@ int b200s_forward_render(const B200sForwardArgs* a, b200s_stream_t stream_) {
     b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;
     b.ranges = im.ranges; b.point_list = bw.vals[final_buf]; b.rec = g.rec; b.background = a->background;
     b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last; b.out_color = a->out_color;
-    rc = launch_blend_fwd(b, blend_fwd_warps(), stream);
+    {
+        ProfScope ps(B200S_STAGE_BLEND_FWD, stream);
+        rc = launch_blend_fwd(b, blend_fwd_warps(), stream);
+    }
     if (rc) return rc;
     B200S_AFTER_LAUNCH(stream, a->debug);
     return 0;
@@ -211,18 +279,24 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
     const int passes = sort_num_passes(d.tiles);
     const int final_buf = passes & 1;
 
+    ProfScope* misc = new ProfScope(B200S_STAGE_MISC, stream);
     if (a->deterministic) {
         B200S_CUDA_OK(cudaMemsetAsync(ws.partial, 0, sizeof(float) * ACC_STRIDE * (size_t)(a->num_rendered > 0 ? a->num_rendered : 1), stream));
     } else {
         B200S_CUDA_OK(cudaMemsetAsync(ws.accum, 0, sizeof(float) * ACC_STRIDE * (size_t)a->P, stream));
     }
+    delete misc;
     if (a->num_rendered > 0) {
         BlendBwdParams b;
         b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;
         b.ranges = im.ranges; b.point_list = bw.vals[final_buf]; b.rec = g.rec; b.point_offsets = g.point_offsets;
         b.background = a->background; b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last;
         b.dL_dpix = a->dL_dout_color; b.accum = ws.accum; b.partial = ws.partial; b.deterministic = a->deterministic;
-        int rc = launch_blend_bwd(b, blend_bwd_warps(), stream);
+        int rc;
+        {
+            ProfScope ps(B200S_STAGE_BLEND_BWD, stream);
+            rc = launch_blend_bwd(b, blend_bwd_warps(), stream);
+        }
         if (rc) return rc;
         B200S_AFTER_LAUNCH(stream, a->debug);
     }
@@ -239,7 +313,11 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
     p.dL_dmeans3D = a->dL_dmeans3D; p.dL_dmeans2D = a->dL_dmeans2D; p.dL_dopacity = a->dL_dopacity;
     p.dL_dsh = a->dL_dsh; p.dL_dscales = a->dL_dscales; p.dL_drotations = a->dL_drotations;
     p.dL_dcolors = a->dL_dcolors; p.dL_dcov3D = a->dL_dcov3D; p.dL_dconic = a->dL_dconic;
-    int rc = launch_preprocess_bwd(p, stream);
+    int rc;
+    {
+        ProfScope ps(B200S_STAGE_PREPROCESS_BWD, stream);
+        rc = launch_preprocess_bwd(p, stream);
+    }
     if (rc) return rc;
     B200S_AFTER_LAUNCH(stream, a->debug);
     return 0;
@@ -258,14 +336,34 @@ size_t b200s_idxmap_workspace_size(int32_t P, int32_t W, int32_t H) {
     return idxmap_workspace_size_impl(P, W, H);
 }
 int b200s_idxmap_forward(const B200sIdxmapArgs* args, b200s_stream_t stream) {
+    ProfScope ps(B200S_STAGE_IDXMAP, (cudaStream_t)stream);
     return idxmap_forward_impl(args, (cudaStream_t)stream);
 }
 int b200s_idxmap_backward(int32_t P, int32_t W, int32_t H, const int32_t* out_idx, const float* grad_feature,
                           float* dL_dfeature_vector, b200s_stream_t stream) {
+    ProfScope ps(B200S_STAGE_IDXMAP_BWD, (cudaStream_t)stream);
     return idxmap_backward_impl(P, W, H, out_idx, grad_feature, dL_dfeature_vector, (cudaStream_t)stream);
 }
 
 }  // extern "C"
+
+extern "C" int b200s_count_pairs(const B200sForwardArgs* a, unsigned long long* counts_dev, b200s_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!a || !counts_dev) return B200S_E_BADARG;
+    B200S_CUDA_OK(cudaMemsetAsync(counts_dev, 0, 3 * sizeof(unsigned long long), stream));
+    if (a->P <= 0) return 0;
+    if (!a->geom_ws || !a->img_ws || !a->bin_ws) return B200S_E_BADARG;
+    const Dims d = dims_of(a->W, a->H, a->tan_fovx, a->tan_fovy);
+    GeomWS g = carve_geom(a->geom_ws, a->P);
+    ImgWS im = carve_img(a->img_ws, a->W, a->H);
+    BinWS bw = carve_bin(a->bin_ws, a->bin_capacity);
+    BlendFwdParams b;
+    b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;
+    b.ranges = im.ranges; b.point_list = bw.vals[sort_num_passes(d.tiles) & 1]; b.rec = g.rec;
+    b.background = a->background; b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last;
+    b.out_color = a->out_color;
+    return launch_count_pairs(b, counts_dev, stream);
+}
 
 // ---------------------------------------------------------------------------- state export
 namespace {
@@ -329,6 +427,7 @@ extern "C" int64_t b200s_export_state(const B200sForwardArgs* a, int32_t which, 
     if (src) {
         if (cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, stream) != cudaSuccess) return B200S_E_BADARG;
     } else {
+        count_launch();
         export_rec_kernel<<<(unsigned)((P + 255) / 256), 256, 0, stream>>>((int)P, g.rec, a->radii, g.clamped, which,
                                                                          (float*)dst, (uint8_t*)dst);
         if (cudaGetLastError() != cudaSuccess) return B200S_E_BADARG;

@@ -376,6 +376,7 @@ int launch_scan(const uint32_t* in, uint32_t* out, int P, uint32_t* status, uint
                 B200sHeader* header, cudaStream_t stream) {
     if (P <= 0) return 0;
     const int tiles = (P + SCAN_TILE - 1) / SCAN_TILE;
+    count_launch();
     scan_tiles_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(in, out, P, status, counters, header);
     return (int)cudaGetLastError();
 }
@@ -413,15 +414,22 @@ int launch_binning(int P, const SplatRec* rec, const uint32_t* offsets, const Bi
     const int passes = sort_num_passes(tiles);
     if (n_hint > capacity) n_hint = capacity;
     if (n_hint < 1) n_hint = 1;
-    B200S_CUDA_OK(cudaMemsetAsync(bw.hist, 0, bw.zero_bytes, stream));
-    B200S_CUDA_OK(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, stream));
+    {
+        ProfScope ps(B200S_STAGE_MISC, stream);
+        B200S_CUDA_OK(cudaMemsetAsync(bw.hist, 0, bw.zero_bytes, stream));
+        B200S_CUDA_OK(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, stream));
+    }
     if (P > 0) {
+        ProfScope ps(B200S_STAGE_EXPAND, stream);
+        count_launch();
         expand_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, rec, offsets, bw.keys[0], bw.vals[0],
                                                                grid_x, header, capacity);
         B200S_AFTER_LAUNCH(stream, debug);
     }
     const int64_t sort_tiles = (n_hint + SORT_TILE - 1) / SORT_TILE;
+    prof_begin(B200S_STAGE_SORT, stream);
     {
+        count_launch(2);
         int hb = (int)((n_hint + 256 * 16 - 1) / (256 * 16));
         if (hb > 148 * 8) hb = 148 * 8;
         if (hb < 1) hb = 1;
@@ -432,6 +440,7 @@ int launch_binning(int P, const SplatRec* rec, const uint32_t* offsets, const Bi
     }
     int cur = 0;
     for (int p = 0; p < passes; ++p) {
+        count_launch();
         sort_onesweep_kernel<<<(unsigned)sort_tiles, SORT_THREADS, SORT_SMEM, stream>>>(
             bw.keys[cur], bw.vals[cur], bw.keys[cur ^ 1], bw.vals[cur ^ 1], header, capacity,
             p * SORT_RADIX_BITS, bw.hist + p * SORT_RADIX,
@@ -439,8 +448,11 @@ int launch_binning(int P, const SplatRec* rec, const uint32_t* offsets, const Bi
         B200S_AFTER_LAUNCH(stream, debug);
         cur ^= 1;
     }
+    prof_end(B200S_STAGE_SORT, stream);
     *final_buf = cur;
     {
+        ProfScope ps(B200S_STAGE_RANGES, stream);
+        count_launch();
         int rb = (int)((n_hint + 255) / 256);
         if (rb > 148 * 16) rb = 148 * 16;
         tile_ranges_kernel<<<rb, 256, 0, stream>>>(bw.keys[cur], header, capacity, ranges);

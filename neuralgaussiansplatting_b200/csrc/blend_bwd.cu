@@ -224,6 +224,7 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
 template <int NW>
 static int launch_blend_bwd_nw(const BlendBwdParams& p, cudaStream_t stream) {
     const int tiles = p.grid_x * p.grid_y;
+    count_launch();
     blend_bwd_kernel<NW><<<tiles, 32 * NW, 0, stream>>>(p);
     return (int)cudaGetLastError();
 }

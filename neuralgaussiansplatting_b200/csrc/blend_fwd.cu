@@ -194,9 +194,56 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     }
 }
 
+// Roofline accounting only: one thread per pixel replays the reference traversal
+// (forward.cu:325-351) and counts traversed / contributing pairs, plus the backward's traversal.
+__global__ void __launch_bounds__(256)
+count_pairs_kernel(const __grid_constant__ BlendFwdParams p, unsigned long long* counts) {
+    const int tile = blockIdx.x;
+    const int tx = tile % p.grid_x, ty = tile / p.grid_x;
+    const int x = tx * TILE + (threadIdx.x & 15), y = ty * TILE + (threadIdx.x >> 4);
+    unsigned long long trav = 0, contrib = 0, bwd = 0;
+    if (x < p.W && y < p.H) {
+        const uint2 range = p.ranges[tile];
+        const float pxf = (float)x, pyf = (float)y;
+        float T = 1.0f;
+        for (uint32_t k = range.x; k < range.y; ++k) {
+            ++trav;
+            const SplatRec* r = p.rec + p.point_list[k];
+            const float4 q0 = r->q0;
+            const float4 q1 = r->q1;
+            const float power = power_ref(fsub(q0.x, pxf), fsub(q0.y, pyf), q0.z, q0.w, q1.x);
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, fmul(q1.y, expf(power)));
+            if (alpha < ALPHA_MIN) continue;
+            const float test_T = fmul(T, fsub(1.0f, alpha));
+            if (test_T < 0.0001f) break;
+            T = test_T;
+            ++contrib;
+        }
+        bwd = p.n_contrib[(size_t)y * p.W + x];
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        trav += __shfl_xor_sync(FULL_MASK, trav, o);
+        contrib += __shfl_xor_sync(FULL_MASK, contrib, o);
+        bwd += __shfl_xor_sync(FULL_MASK, bwd, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&counts[0], trav); atomicAdd(&counts[1], contrib); atomicAdd(&counts[2], bwd);
+    }
+}
+
+int launch_count_pairs(const BlendFwdParams& p, unsigned long long* counts, cudaStream_t stream) {
+    const int tiles = p.grid_x * p.grid_y;
+    if (tiles <= 0) return 0;
+    count_launch();
+    count_pairs_kernel<<<tiles, 256, 0, stream>>>(p, counts);
+    return (int)cudaGetLastError();
+}
+
 template <int NW>
 static int launch_blend_fwd_nw(const BlendFwdParams& p, cudaStream_t stream) {
     const int tiles = p.grid_x * p.grid_y;
+    count_launch();
     blend_fwd_kernel<NW><<<tiles, 32 * NW, 0, stream>>>(p);
     return (int)cudaGetLastError();
 }

@@ -189,10 +189,12 @@ int idxmap_forward_impl(const B200sIdxmapArgs* a, cudaStream_t stream) {
     if (a->ws_bytes < idxmap_workspace_size_impl(a->P, a->W, a->H)) return B200S_E_WORKSPACE;
     IdxWS ws = carve_idx(a->ws, a->W, a->H);
     B200S_CUDA_OK(cudaMemsetAsync(ws.zbuf, 0xff, 8 * npix, stream));
+    count_launch();
     idx_splat_kernel<<<(a->P + 255) / 256, 256, 0, stream>>>(a->P, a->W, a->H, a->means3D, a->viewmatrix,
                                                            a->projmatrix, a->radii, ws.zbuf, a->num_rendered_dev);
     B200S_AFTER_LAUNCH(stream, a->debug);
     const unsigned blocks = (unsigned)((npix + 255) / 256);
+    count_launch();
     idx_resolve_kernel<<<blocks, 256, 0, stream>>>(a->P, a->W, a->H, ws.zbuf, a->means3D, a->campos,
                                                    a->feature_vector, a->out_idx, a->out_color, a->out_depth,
                                                    a->out_feature);
@@ -208,6 +210,7 @@ int idxmap_backward_impl(int P, int W, int H, const int32_t* out_idx, const floa
     const int64_t npix = (int64_t)W * H;
     B200S_CUDA_OK(cudaMemsetAsync(dL_dfeature_vector, 0, 4 * (size_t)NFEAT * P, stream));
     const unsigned blocks = (unsigned)((npix + 255) / 256);
+    count_launch();
     idx_feature_backward_kernel<<<blocks, 256, 0, stream>>>(P, npix, out_idx, grad_feature, dL_dfeature_vector);
     return (int)cudaGetLastError();
 }

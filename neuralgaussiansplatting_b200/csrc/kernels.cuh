@@ -84,6 +84,17 @@ struct PreprocessBwdParams {
     float* dL_dconic;
 };
 
+// measurement hooks (api.cu)
+void prof_begin(int stage, cudaStream_t stream);
+void prof_end(int stage, cudaStream_t stream);
+void count_launch(int n = 1);
+struct ProfScope {
+    int stage; cudaStream_t stream;
+    ProfScope(int st, cudaStream_t s) : stage(st), stream(s) { prof_begin(stage, stream); }
+    ~ProfScope() { prof_end(stage, stream); }
+};
+int launch_count_pairs(const BlendFwdParams& p, unsigned long long* counts, cudaStream_t stream);
+
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
 int launch_scan(const uint32_t* in, uint32_t* out, int P, uint32_t* status, uint32_t* counters,

@@ -242,8 +242,10 @@ int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream) {
                                                (int)PRE_SMEM_SH16));
             attr_set = true;
         }
+        count_launch();
         preprocess_fwd_kernel<true><<<blocks, PRE_THREADS, PRE_SMEM_SH16, stream>>>(p);
     } else {
+        count_launch();
         preprocess_fwd_kernel<false><<<blocks, PRE_THREADS, 0, stream>>>(p);
     }
     return (int)cudaGetLastError();
@@ -252,6 +254,7 @@ int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream) {
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,
                         cudaStream_t stream) {
     if (P <= 0) return 0;
+    count_launch();
     mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, view, present);
     return (int)cudaGetLastError();
 }

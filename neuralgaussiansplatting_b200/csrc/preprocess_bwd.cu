@@ -366,8 +366,10 @@ int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream) {
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PB_SMEM_SH16));
             attr_set = true;
         }
+        count_launch();
         preprocess_bwd_kernel<true><<<blocks, PB_THREADS, PB_SMEM_SH16, stream>>>(p);
     } else {
+        count_launch();
         preprocess_bwd_kernel<false><<<blocks, PB_THREADS, 0, stream>>>(p);
     }
     return (int)cudaGetLastError();

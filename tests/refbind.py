@@ -97,18 +97,20 @@ class RefDGR:
 
     def forward(self, *, bg, means3D, opacities, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, W, H,
                 shs=None, colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None, degree=3,
-                scale_modifier=1.0, prefiltered=False, debug=False):
+                scale_modifier=1.0, prefiltered=False, debug=False, sync=True):
         dev = means3D.device
         P = means3D.shape[0]
         M = shs.shape[1] if shs is not None and shs.numel() else 0
         out = torch.zeros(3, H, W, dtype=torch.float32, device=dev)
         radii = torch.zeros(P, dtype=torch.int32, device=dev)
-        torch.cuda.synchronize(dev)
+        if sync:   # the reference launches on the legacy default stream (= torch's default stream)
+            torch.cuda.synchronize(dev)
         R = self.lib.ref_dgr_forward(self.h, P, degree, M, _p(bg), W, H, _p(means3D), _p(shs), _p(colors_precomp),
                                      _p(opacities), _p(scales), scale_modifier, _p(rotations), _p(cov3D_precomp),
                                      _p(viewmatrix), _p(projmatrix), _p(campos), tan_fovx, tan_fovy,
                                      int(prefiltered), out.data_ptr(), radii.data_ptr(), int(debug))
-        torch.cuda.synchronize(dev)
+        if sync:
+            torch.cuda.synchronize(dev)
         if R < 0:
             raise RuntimeError("reference forward failed")
         self.R, self.P, self.W, self.H, self.M, self.D = R, P, W, H, M, degree
@@ -116,13 +118,14 @@ class RefDGR:
 
     def backward(self, *, bg, means3D, radii, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, dL_dpix,
                  shs=None, colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None,
-                 scale_modifier=1.0, debug=False):
+                 scale_modifier=1.0, debug=False, sync=True):
         dev = means3D.device
         P, M = self.P, self.M
         z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)  # noqa: E731
         g = dict(means2D=z(P, 3), conic=z(P, 2, 2), opacity=z(P, 1), colors=z(P, 3), means3D=z(P, 3),
                  cov3D=z(P, 6), sh=z(P, M, 3), scales=z(P, 3), rotations=z(P, 4))
-        torch.cuda.synchronize(dev)
+        if sync:
+            torch.cuda.synchronize(dev)
         rc = self.lib.ref_dgr_backward(self.h, P, self.D, M, self.R, _p(bg), self.W, self.H, _p(means3D), _p(shs),
                                        _p(colors_precomp), _p(scales), scale_modifier, _p(rotations),
                                        _p(cov3D_precomp), _p(viewmatrix), _p(projmatrix), _p(campos), tan_fovx,
@@ -130,7 +133,8 @@ class RefDGR:
                                        g["conic"].data_ptr(), g["opacity"].data_ptr(), g["colors"].data_ptr(),
                                        g["means3D"].data_ptr(), g["cov3D"].data_ptr(), _p(g["sh"]),
                                        g["scales"].data_ptr(), g["rotations"].data_ptr(), int(debug))
-        torch.cuda.synchronize(dev)
+        if sync:
+            torch.cuda.synchronize(dev)
         if rc != 0:
             raise RuntimeError("reference backward failed")
         return g
