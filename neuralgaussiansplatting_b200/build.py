@@ -27,7 +27,7 @@ NVCC_FLAGS = [
     "--expt-relaxed-constexpr", "--extended-lambda",
     "-Xcompiler", "-fPIC",
     "-Xptxas", "-v",
-]
+] + (os.environ.get("B200S_NVCC_EXTRA", "").split())
 
 
 def find_nvcc() -> str:

@@ -387,6 +387,16 @@ __global__ void export_rec_kernel(int P, const SplatRec* rec, const int* radii, 
         }
     }
 }
+// The sorted 64-bit keys are not materialised by the two-level sort (the blend only needs the
+// sorted Gaussian ids): rebuild them as tile << 32 | depth bits of the sorted ids.
+__global__ void export_keys_kernel(int tiles, const uint2* ranges, const uint32_t* point_list, const SplatRec* rec,
+                                   unsigned long long* dst) {
+    const int tile = blockIdx.x;
+    if (tile >= tiles) return;
+    const uint2 r = ranges[tile];
+    for (uint32_t i = r.x + threadIdx.x; i < r.y; i += blockDim.x)
+        dst[i] = ((unsigned long long)tile << 32) | (unsigned long long)__float_as_uint(rec[point_list[i]].q2.y);
+}
 }  // namespace
 
 extern "C" int64_t b200s_export_state(const B200sForwardArgs* a, int32_t which, int64_t num_rendered, void* dst,
@@ -417,7 +427,16 @@ extern "C" int64_t b200s_export_state(const B200sForwardArgs* a, int32_t which, 
             BinWS bw = carve_bin(a->bin_ws, a->bin_capacity);
             const int fb = sort_num_passes(d.tiles) & 1;
             if (which == B200S_STATE_POINT_LIST) { src = bw.vals[fb]; bytes = 4 * num_rendered; }
-            else { src = bw.keys[fb]; bytes = 8 * num_rendered; }
+            else {
+                bytes = 8 * num_rendered;
+                if (bytes > dst_bytes) return B200S_E_WORKSPACE;
+                if (bytes == 0) return 0;
+                count_launch();
+                export_keys_kernel<<<d.tiles, 256, 0, stream>>>(d.tiles, im.ranges, bw.vals[fb], g.rec,
+                                                                (unsigned long long*)dst);
+                if (cudaGetLastError() != cudaSuccess) return B200S_E_BADARG;
+                return bytes;
+            }
             break;
         }
         default: return B200S_E_BADARG;

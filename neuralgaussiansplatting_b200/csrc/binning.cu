@@ -13,9 +13,16 @@
 //             slots to consecutive threads (binary search in shared memory), so a Gaussian
 //             covering 2,000 tiles no longer serialises one thread (the reference loops
 //             per thread, rasterizer_impl.cu:98-109) and all 12-B stores coalesce.
-//  * sort:    onesweep: one histogram pass over the keys for all digits, then one
-//             read+write pass per 8-bit digit with a chained look-back over 4,096-key tiles;
-//             in-tile ranking by warp match, stable by construction.
+//  * sort:    two levels. (1) onesweep over the TILE bits only (bits [32, 32+bit), two 8-bit
+//             passes for up to 65,536 tiles): one histogram pass, then one read+write pass per
+//             digit with a chained look-back over 4,096-key blocks; in-block ranking by warp
+//             match, stable by construction. (2) every tile's run — now contiguous, in
+//             insertion (= Gaussian index) order — is sorted on the 32 depth bits by ONE CTA
+//             entirely in shared memory (4 stable 8-bit passes, no HBM traffic besides one read
+//             of the run and one 4-byte write per instance). Runs longer than the shared-memory
+//             capacity take the same stable passes through global memory. The result is
+//             bit-identical to the reference's single 6-pass sort of the 45-bit key
+//             (any stable sort on those bits is), at ~64 instead of ~152 B/instance.
 //  * N (num_rendered) is read from device memory by every kernel: no host round trip is
 //    needed between the stages (the reference blocks on a 4-byte D2H, rasterizer_impl.cu:281).
 
@@ -178,7 +185,7 @@ expand_keys_kernel(int P, const SplatRec* __restrict__ rec, const uint32_t* __re
 // ------------------------------------------------------------------------------- sort
 __global__ void __launch_bounds__(256)
 sort_histogram_kernel(const uint64_t* __restrict__ keys, const B200sHeader* header, int64_t capacity,
-                      int passes, uint32_t* __restrict__ hist) {
+                      int first_shift, int passes, uint32_t* __restrict__ hist) {
     __shared__ uint32_t s_h[SORT_MAX_PASSES * SORT_RADIX];
     uint32_t n = header->num_rendered;
     if ((int64_t)n > capacity) n = 0;
@@ -188,7 +195,7 @@ sort_histogram_kernel(const uint64_t* __restrict__ keys, const B200sHeader* head
     for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
         const uint64_t key = keys[i];
         for (int p = 0; p < passes; ++p)
-            atomicAdd(&s_h[p * SORT_RADIX + (uint32_t)((key >> (p * SORT_RADIX_BITS)) & (SORT_RADIX - 1))], 1u);
+            atomicAdd(&s_h[p * SORT_RADIX + (uint32_t)((key >> (first_shift + p * SORT_RADIX_BITS)) & (SORT_RADIX - 1))], 1u);
     }
     __syncthreads();
     for (int i = threadIdx.x; i < passes * SORT_RADIX; i += 256) {
@@ -263,16 +270,22 @@ sort_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
     }
     uint32_t* wc = s_cnt + warp * SORT_CNT_STRIDE;
     const uint32_t lt = lanemask_lt();
+    {
+        uint32_t peers[SORT_ITEMS];   // independent MATCHes issued back to back (long latency)
 #pragma unroll
-    for (int k = 0; k < SORT_ITEMS; ++k) {
-        const uint32_t d = dr[k];
-        const uint32_t peers = __match_any_sync(FULL_MASK, d);
-        const int leader = __ffs(peers) - 1;
-        uint32_t old = 0;
-        if (lane == leader) { old = wc[d]; wc[d] = old + __popc(peers); }
-        old = __shfl_sync(FULL_MASK, old, leader);
-        dr[k] = d | ((old + __popc(peers & lt)) << 16);
-        __syncwarp();
+        for (int k = 0; k < SORT_ITEMS; ++k) peers[k] = digit_peers(dr[k]);
+#pragma unroll
+        for (int k = 0; k < SORT_ITEMS; ++k) {
+            // every lane reads its digit's running count (same-address reads broadcast), then the
+            // lowest peer lane alone bumps it: no FLO/BREV/SHFL on the critical path
+            const uint32_t d = dr[k];
+            const uint32_t before = peers[k] & lt;
+            const uint32_t old = wc[d];
+            __syncwarp();
+            if (before == 0u) wc[d] = old + __popc(peers[k]);
+            dr[k] = d | ((old + __popc(before)) << 16);
+            __syncwarp();
+        }
     }
     __syncthreads();
 
@@ -371,6 +384,191 @@ tile_ranges_kernel(const uint64_t* __restrict__ keys, const B200sHeader* header,
     }
 }
 
+// -------------------------------------------------------------------- per-tile depth sort
+// One CTA per tile sorts the tile's run (contiguous after the tile-bit passes, in insertion
+// order) on the 32 depth bits with 4 stable 8-bit LSD passes.
+constexpr int TS_THREADS = 256;
+constexpr int TS_WARPS = TS_THREADS / 32;
+constexpr int TS_ITEMS = 16;
+constexpr int TS_CAP = TS_THREADS * TS_ITEMS;          // 4,096 entries sorted entirely in shared memory
+constexpr int TS_CNT_STRIDE = 257;                     // + sentinel digit for padding lanes
+constexpr size_t TS_SMEM = (size_t)TS_CAP * 4 * 4 + (size_t)TS_WARPS * TS_CNT_STRIDE * 4 + 257 * 4 + 64;
+
+// Stable ranking of up to TS_ITEMS items per thread (warp-striped: item k of lane l of warp w is
+// element w*chunk + k*32 + l) by the 8-bit digit; leaves digit | rank << 16 in dr[] and the
+// per-warp digit counts in s_cnt[warp][*].
+__device__ __forceinline__ void ts_rank(uint32_t (&dr)[TS_ITEMS], int kmax, uint32_t* wc, uint32_t lt) {
+    // all matches first: MATCH has a long latency (the dominant stall of this kernel when each one
+    // was consumed immediately), and they are independent of the counter updates below
+    uint32_t peers[TS_ITEMS];
+#pragma unroll
+    for (int k = 0; k < TS_ITEMS; ++k) peers[k] = (k < kmax) ? digit_peers(dr[k]) : 0u;
+#pragma unroll
+    for (int k = 0; k < TS_ITEMS; ++k) {
+        if (k < kmax) {
+            // every lane reads its digit's running count (same-address reads broadcast), then the
+            // lowest peer lane alone bumps it: no FLO/BREV/SHFL on the critical path
+            const uint32_t d = dr[k];
+            const uint32_t before = peers[k] & lt;
+            const uint32_t old = wc[d];
+            __syncwarp();
+            if (before == 0u) wc[d] = old + __popc(peers[k]);
+            dr[k] = d | ((old + __popc(before)) << 16);
+            __syncwarp();
+        }
+    }
+}
+
+// Thread d (< 256): exclusive prefix of digit d over the warps (written back to s_cnt) and the
+// digit's total; then the block-exclusive scan over digits -> returns this digit's start.
+__device__ __forceinline__ uint32_t ts_digit_scan(uint32_t* s_cnt, uint32_t* s_wsum, uint32_t& count) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    count = 0;
+#pragma unroll
+    for (int w = 0; w < TS_WARPS; ++w) {
+        const uint32_t t = s_cnt[w * TS_CNT_STRIDE + tid];
+        s_cnt[w * TS_CNT_STRIDE + tid] = count;
+        count += t;
+    }
+    uint32_t incl = count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULL_MASK, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
+    uint32_t wex = 0;
+    for (int w = 0; w < warp; ++w) wex += s_wsum[w];
+    return wex + incl - count;
+}
+
+__global__ void __launch_bounds__(TS_THREADS)
+tile_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint64_t* __restrict__ keys_tmp,
+                 uint32_t* __restrict__ vals_tmp, const uint2* __restrict__ ranges) {
+    extern __shared__ __align__(16) unsigned char ts_raw[];
+    uint32_t* s_key = reinterpret_cast<uint32_t*>(ts_raw);          // [2][TS_CAP] depth bits
+    uint32_t* s_val = s_key + 2 * TS_CAP;                           // [2][TS_CAP]
+    uint32_t* s_cnt = s_val + 2 * TS_CAP;                           // [TS_WARPS][257]
+    uint32_t* s_dstart = s_cnt + TS_WARPS * TS_CNT_STRIDE;          // [257]
+    uint32_t* s_wsum = s_dstart + 257;                              // [8]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint2 range = ranges[blockIdx.x];
+    const uint32_t n = range.y - range.x;
+    if (n <= 1) return;
+    const uint32_t lt = lanemask_lt();
+    uint32_t* wc = s_cnt + warp * TS_CNT_STRIDE;
+    uint32_t dr[TS_ITEMS];
+
+    if (n <= (uint32_t)TS_CAP) {
+        // ---- shared-memory path
+        for (uint32_t i = tid; i < n; i += TS_THREADS) {
+            s_key[i] = (uint32_t)keys[range.x + i];
+            s_val[i] = vals[range.x + i];
+        }
+        const uint32_t chunk = ((n + TS_THREADS - 1) / TS_THREADS) * 32;   // items per warp
+        const int kmax = (int)(chunk / 32);
+        const uint32_t wbase = warp * chunk + lane;
+        int cur = 0;
+        for (int pass = 0; pass < 4; ++pass) {
+            const int shift = pass * 8;
+            for (int i = tid; i < TS_WARPS * TS_CNT_STRIDE; i += TS_THREADS) s_cnt[i] = 0;
+            __syncthreads();
+            const uint32_t* kin = s_key + cur * TS_CAP;
+#pragma unroll
+            for (int k = 0; k < TS_ITEMS; ++k) {
+                const uint32_t i = wbase + k * 32;
+                dr[k] = (k < kmax && i < n) ? ((kin[i] >> shift) & 255u) : 256u;
+            }
+            ts_rank(dr, kmax, wc, lt);
+            __syncthreads();
+            uint32_t count;
+            const uint32_t dstart = ts_digit_scan(s_cnt, s_wsum, count);
+            s_dstart[tid] = dstart;
+            // a pass whose digit is the same for every entry is the identity permutation: skip it
+            const int uniform = __syncthreads_or(count == n);
+            if (!uniform) {
+                const uint32_t* vin = s_val + cur * TS_CAP;
+                uint32_t* kout = s_key + (cur ^ 1) * TS_CAP;
+                uint32_t* vout = s_val + (cur ^ 1) * TS_CAP;
+#pragma unroll
+                for (int k = 0; k < TS_ITEMS; ++k) {
+                    const uint32_t i = wbase + k * 32;
+                    if (k < kmax && i < n) {
+                        const uint32_t d = dr[k] & 0xffffu;
+                        const uint32_t pos = s_dstart[d] + wc[d] + (dr[k] >> 16);
+                        kout[pos] = kin[i];
+                        vout[pos] = vin[i];
+                    }
+                }
+                cur ^= 1;
+            }
+            __syncthreads();
+        }
+        const uint32_t* vfin = s_val + cur * TS_CAP;
+        for (uint32_t i = tid; i < n; i += TS_THREADS) vals[range.x + i] = vfin[i];
+        return;
+    }
+
+    // ---- long runs: the same stable passes through global memory (this CTA only), ping-pong
+    // between the run's own slots and the same slots of the spare buffers; 4 passes end in place.
+    uint64_t* kin = keys + range.x;  uint32_t* vin = vals + range.x;
+    uint64_t* kout = keys_tmp + range.x;  uint32_t* vout = vals_tmp + range.x;
+    uint32_t* s_base = s_key;      // [256] running destination of each digit (shared-memory reuse)
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = pass * 8;
+        s_base[tid] = 0;
+        __syncthreads();
+        for (uint32_t i = tid; i < n; i += TS_THREADS) atomicAdd(&s_base[(uint32_t)(kin[i] >> shift) & 255u], 1u);
+        __syncthreads();
+        {
+            const uint32_t c = s_base[tid];
+            uint32_t incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(FULL_MASK, incl, o);
+                if (lane >= o) incl += t;
+            }
+            if (lane == 31) s_wsum[warp] = incl;
+            __syncthreads();
+            uint32_t wex = 0;
+            for (int w = 0; w < warp; ++w) wex += s_wsum[w];
+            s_base[tid] = wex + incl - c;
+        }
+        __syncthreads();
+        for (uint32_t c0 = 0; c0 < n; c0 += TS_CAP) {
+            for (int i = tid; i < TS_WARPS * TS_CNT_STRIDE; i += TS_THREADS) s_cnt[i] = 0;
+            __syncthreads();
+            const uint32_t wbase = c0 + warp * (32 * TS_ITEMS) + lane;
+#pragma unroll
+            for (int k = 0; k < TS_ITEMS; ++k) {
+                const uint32_t i = wbase + k * 32;
+                dr[k] = i < n ? ((uint32_t)(kin[i] >> shift) & 255u) : 256u;
+            }
+            ts_rank(dr, TS_ITEMS, wc, lt);
+            __syncthreads();
+            uint32_t count;
+            (void)ts_digit_scan(s_cnt, s_wsum, count);
+#pragma unroll
+            for (int k = 0; k < TS_ITEMS; ++k) {
+                const uint32_t i = wbase + k * 32;
+                if (i < n) {
+                    const uint32_t d = dr[k] & 0xffffu;
+                    const uint32_t pos = s_base[d] + wc[d] + (dr[k] >> 16);
+                    kout[pos] = kin[i];
+                    vout[pos] = vin[i];
+                }
+            }
+            __syncthreads();
+            s_base[tid] += count;
+            __syncthreads();
+        }
+        uint64_t* tk = kin; kin = kout; kout = tk;
+        uint32_t* tv = vin; vin = vout; vout = tv;
+    }
+}
+
 // ------------------------------------------------------------------------ host launchers
 int launch_scan(const uint32_t* in, uint32_t* out, int P, uint32_t* status, uint32_t* counters,
                 B200sHeader* header, cudaStream_t stream) {
@@ -393,9 +591,12 @@ static uint32_t higher_msb(uint32_t n) {
     return msb;
 }
 
+// Number of onesweep passes over the TILE bits [32, 32+bit); the sorted run lives in ping-pong
+// buffer (passes & 1).
 int sort_num_passes(int tiles) {
-    const int bits = 32 + (int)higher_msb((uint32_t)tiles);
-    return (bits + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+    const int bits = (int)higher_msb((uint32_t)tiles);
+    const int p = (bits + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+    return p < 1 ? 1 : p;
 }
 
 // Runs expand + sort + ranges. `n_hint` bounds the number of instances for grid sizing
@@ -409,6 +610,8 @@ int launch_binning(int P, const SplatRec* rec, const uint32_t* offsets, const Bi
     if (!attr_set) {
         B200S_CUDA_OK(cudaFuncSetAttribute(sort_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)SORT_SMEM));
+        B200S_CUDA_OK(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)TS_SMEM));
         attr_set = true;
     }
     const int passes = sort_num_passes(tiles);
@@ -433,7 +636,7 @@ int launch_binning(int P, const SplatRec* rec, const uint32_t* offsets, const Bi
         int hb = (int)((n_hint + 256 * 16 - 1) / (256 * 16));
         if (hb > 148 * 8) hb = 148 * 8;
         if (hb < 1) hb = 1;
-        sort_histogram_kernel<<<hb, 256, 0, stream>>>(bw.keys[0], header, capacity, passes, bw.hist);
+        sort_histogram_kernel<<<hb, 256, 0, stream>>>(bw.keys[0], header, capacity, 32, passes, bw.hist);
         B200S_AFTER_LAUNCH(stream, debug);
         sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, stream>>>(bw.hist);
         B200S_AFTER_LAUNCH(stream, debug);
@@ -443,7 +646,7 @@ int launch_binning(int P, const SplatRec* rec, const uint32_t* offsets, const Bi
         count_launch();
         sort_onesweep_kernel<<<(unsigned)sort_tiles, SORT_THREADS, SORT_SMEM, stream>>>(
             bw.keys[cur], bw.vals[cur], bw.keys[cur ^ 1], bw.vals[cur ^ 1], header, capacity,
-            p * SORT_RADIX_BITS, bw.hist + p * SORT_RADIX,
+            32 + p * SORT_RADIX_BITS, bw.hist + p * SORT_RADIX,
             bw.lookback + (size_t)p * bw.sort_tiles * SORT_RADIX, counters + CTR_SORT_TICKET0 + p);
         B200S_AFTER_LAUNCH(stream, debug);
         cur ^= 1;
@@ -456,6 +659,14 @@ int launch_binning(int P, const SplatRec* rec, const uint32_t* offsets, const Bi
         int rb = (int)((n_hint + 255) / 256);
         if (rb > 148 * 16) rb = 148 * 16;
         tile_ranges_kernel<<<rb, 256, 0, stream>>>(bw.keys[cur], header, capacity, ranges);
+        B200S_AFTER_LAUNCH(stream, debug);
+    }
+    {
+        // depth order inside every tile (ranges are all-zero when the binning overflowed: no work)
+        ProfScope ps(B200S_STAGE_SORT, stream);
+        count_launch();
+        tile_sort_kernel<<<tiles, TS_THREADS, TS_SMEM, stream>>>(bw.keys[cur], bw.vals[cur], bw.keys[cur ^ 1],
+                                                                bw.vals[cur ^ 1], ranges);
         B200S_AFTER_LAUNCH(stream, debug);
     }
     return 0;
