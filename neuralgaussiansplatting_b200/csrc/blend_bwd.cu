@@ -17,48 +17,67 @@
 // preprocess_bwd turns them into dL/dmean2D = -(a*S1+b*S2, c*S2+b*S1)*(W/2,H/2) and
 // dL/dconic = -0.5*(Sxx, Sxy, Syy)   (backward.cu:538-554 factored).
 
-#include "kernels.cuh"
+#include "blend_common.cuh"
 
 namespace b200s {
 
 
-constexpr float ALPHA_MIN_B = 1.0f / 255.0f;
+constexpr float ALPHA_MIN_B = BLEND_ALPHA_MIN;
 
-__device__ __forceinline__ bool splat_reaches_tile_b(float x, float y, float a, float b, float c, float op,
-                                                     float X0, float Y0, float X1, float Y1, float& thr) {
-    thr = -logf(255.0f * op) - 1e-4f;
-    if (op < ALPHA_MIN_B) return false;
-    const float ex = fminf(fmaxf(x, X0), X1) - x;
-    const float ey = fminf(fmaxf(y, Y0), Y1) - y;
-    if (ex == 0.0f && ey == 0.0f) return true;
-    if (!(a > 0.0f && c > 0.0f && a * c > b * b)) return true;
-    const float dx0 = X0 - x, dx1 = X1 - x, dy0 = Y0 - y, dy1 = Y1 - y;
-    float qmin = 3.0e38f;
-    if (ex != 0.0f) {
-        const float dy = fminf(fmaxf(__fdividef(-b * ex, c), dy0), dy1);
-        qmin = fminf(qmin, a * ex * ex + 2.0f * b * ex * dy + c * dy * dy);
+// Sum of nine per-lane partials over the warp. The first eight are reduced with a transposing
+// butterfly (4 + 2 + 1 + 1 + 1 = 9 shuffles instead of 40): after it lane l holds the warp total
+// of value ((l >> 4) & 1) * 4 + ((l >> 3) & 1) * 2 + ((l >> 2) & 1). The ninth takes the plain
+// five steps. Returns this lane's value and its index in `which` (-1: nothing to write; only
+// lanes 0, 4, .., 28 and lane 1 — which carries the ninth — write).
+__device__ __forceinline__ float reduce9(float (&acc)[9], int lane, int& which) {
+    {
+        const bool hi = lane & 16;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float send = hi ? acc[i] : acc[i + 4];
+            const float keep = hi ? acc[i + 4] : acc[i];
+            acc[i] = keep + __shfl_xor_sync(FULL_MASK, send, 16);
+        }
     }
-    if (ey != 0.0f) {
-        const float dx = fminf(fmaxf(__fdividef(-b * ey, a), dx0), dx1);
-        qmin = fminf(qmin, a * dx * dx + 2.0f * b * dx * ey + c * ey * ey);
+    {
+        const bool hi = lane & 8;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const float send = hi ? acc[i] : acc[i + 2];
+            const float keep = hi ? acc[i + 2] : acc[i];
+            acc[i] = keep + __shfl_xor_sync(FULL_MASK, send, 8);
+        }
     }
-    const float mx = fmaxf(fabsf(dx0), fabsf(dx1)), my = fmaxf(fabsf(dy0), fabsf(dy1));
-    const float S = a * mx * mx + 2.0f * fabsf(b) * mx * my + c * my * my;
-    return !(qmin > -2.0f * thr + 4e-6f * S + 1e-4f);
+    {
+        const bool hi = lane & 4;
+        const float send = hi ? acc[0] : acc[1];
+        const float keep = hi ? acc[1] : acc[0];
+        acc[0] = keep + __shfl_xor_sync(FULL_MASK, send, 4);
+    }
+    acc[0] += __shfl_xor_sync(FULL_MASK, acc[0], 2);
+    acc[0] += __shfl_xor_sync(FULL_MASK, acc[0], 1);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[8] += __shfl_xor_sync(FULL_MASK, acc[8], o);
+    which = -1;
+    if ((lane & 3) == 0) which = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+    if (lane == 1) which = 8;
+    return lane == 1 ? acc[8] : acc[0];
 }
 
-template <int NW>
+template <int NW, int SPT>
 __global__ void __launch_bounds__(32 * NW)
 blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
-    constexpr int PX = 8 / NW;
-    constexpr int NX = PX >= 2 ? 2 : 1;
-    constexpr int NY = PX >= 2 ? PX / 2 : 1;
-    constexpr int BATCH = 32 * NW;
+    using WB = WarpBlocks<NW>;
+    constexpr int PX = WB::PX, NX = WB::NX, NY = WB::NY;
+    constexpr int NT = 32 * NW;
+    constexpr int BATCH = NT * SPT;
+    constexpr int NSEG = NW * SPT;
 
-    __shared__ float4 s_a[2][BATCH];           // x, y, conic a, conic b
-    __shared__ float4 s_b[2][BATCH];           // conic c, opacity, power threshold, list pos
-    __shared__ float4 s_c[2][BATCH];           // r, g, b, destination (Gaussian id | slot)
-    __shared__ int s_cnt[2][NW];
+    __shared__ float4 s_q0[2][BATCH];          // x, y, conic a, conic b
+    __shared__ float4 s_q1[2][BATCH];          // conic c, opacity, r, g
+    __shared__ float4 s_q2[2][BATCH];          // b, power threshold, list pos, destination
+    __shared__ uint16_t s_idx[BATCH];
+    __shared__ int s_cnt[NSEG];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x;
@@ -68,24 +87,27 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
     const int n = min((int)(range.y - range.x), (int)p.tile_last[tile]);
     if (n <= 0) return;
 
-    float pxf[NX], pyf[NY];
+    float pxf[NX], pyf[NY], bx0[NX], by0[NY];
     int pix_x[NX], pix_y[NY];
-    const int b0 = warp * PX;
 #pragma unroll
     for (int i = 0; i < NX; ++i) {
-        pix_x[i] = tile_x * TILE + (((b0 + i) & 1) * 8) + (lane & 7);
+        const int x0 = tile_x * TILE + WB::col_block(warp, i) * 8;
+        bx0[i] = (float)x0;
+        pix_x[i] = x0 + (lane & 7);
         pxf[i] = (float)pix_x[i];
     }
 #pragma unroll
     for (int i = 0; i < NY; ++i) {
-        pix_y[i] = tile_y * TILE + (((b0 + 2 * i) >> 1) * 4) + (lane >> 3);
+        const int y0 = tile_y * TILE + WB::row_block(warp, i) * 4;
+        by0[i] = (float)y0;
+        pix_y[i] = y0 + (lane >> 3);
         pyf[i] = (float)pix_y[i];
     }
 
     const float bg0 = p.background[0], bg1 = p.background[1], bg2 = p.background[2];
     const size_t plane = (size_t)p.W * p.H;
     float T[PX], Tf_bg[PX], Ar[PX], Ag[PX], Ab[PX], gr[PX], gg[PX], gb[PX];
-    uint32_t lastc[PX];
+    uint32_t lastc[PX], blocklast[PX];
 #pragma unroll
     for (int s = 0; s < PX; ++s) {
         const bool inside = pix_x[s % NX] < p.W && pix_y[s / NX] < p.H;
@@ -98,6 +120,7 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
         // -T_final * (bg . dL/dpix): the background term of dL/dalpha (backward.cu:531-534)
         Tf_bg[s] = -T[s] * (bg0 * gr[s] + bg1 * gg[s] + bg2 * gb[s]);
         Ar[s] = Ag[s] = Ab[s] = 0.0f;
+        blocklast[s] = __reduce_max_sync(FULL_MASK, lastc[s]);   // no pixel of block s goes deeper
     }
 
     const float X0 = (float)(tile_x * TILE), Y0 = (float)(tile_y * TILE);
@@ -105,49 +128,133 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
 
     const int nb = (n + BATCH - 1) / BATCH;
     const uint32_t* list = p.point_list + range.x;
-    // batch b covers list positions [n-(b+1)*BATCH, n-b*BATCH); thread t takes position
-    // n-b*BATCH-BATCH+t so that warp/lane order stays list order.
-    auto pos_of = [&](int b) { return n - (b + 1) * BATCH + tid; };
-    int pos0 = pos_of(0);
-    int id0 = (pos0 >= 0) ? (int)list[pos0] : -1;
-    int pos1 = pos_of(1);
-    int id1 = (pos1 >= 0) ? (int)list[pos1] : -1;
-    float4 q0 = make_float4(0, 0, 0, 0), q1 = q0, q2 = q0;
-    if (id0 >= 0) { const SplatRec* r = p.rec + id0; q0 = r->q0; q1 = r->q1; q2 = r->q2; }
+    const uint32_t lt = lanemask_lt();
+    // batch b covers list positions [n-(b+1)*BATCH, n-b*BATCH); element i of the batch is
+    // position n-(b+1)*BATCH+i, so element order stays list order.
+    int idc[SPT], idn[SPT];
+#pragma unroll
+    for (int k = 0; k < SPT; ++k) {
+        const int i = k * NT + tid;
+        const int pos = n - BATCH + i;
+        idc[k] = (pos >= 0) ? (int)list[pos] : -1;
+        if (idc[k] >= 0) {
+            const SplatRec* r = p.rec + idc[k];
+            cp_async16(&s_q0[0][i], &r->q0);
+            cp_async16(&s_q1[0][i], &r->q1);
+            cp_async16(&s_q2[0][i], &r->q2);
+        }
+    }
+    cp_async_commit();
+#pragma unroll
+    for (int k = 0; k < SPT; ++k) {
+        const int pos = n - 2 * BATCH + k * NT + tid;
+        idn[k] = (pos >= 0) ? (int)list[pos] : -1;
+    }
 
     for (int b = 0; b < nb; ++b) {
         const int buf = b & 1;
-        const int pos2 = pos_of(b + 2);
-        const int id2 = (pos2 >= 0) ? (int)list[pos2] : -1;
-        float4 n0 = make_float4(0, 0, 0, 0), n1 = n0, n2 = n0;
-        if (id1 >= 0) { const SplatRec* r = p.rec + id1; n0 = r->q0; n1 = r->q1; n2 = r->q2; }
-
-        float thr;
-        const bool keep = (id0 >= 0) && splat_reaches_tile_b(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, X0, Y0, X1, Y1, thr);
-        const uint32_t ballot = __ballot_sync(FULL_MASK, keep);
-        if (keep) {
-            uint32_t dest = (uint32_t)id0;
-            if (p.deterministic) {
-                // slot of this instance in the unsorted (Gaussian-major, tile-minor) order
-                const uint32_t rmin = __float_as_uint(q2.z), rwh = __float_as_uint(q2.w);
-                const uint32_t first = id0 == 0 ? 0u : p.point_offsets[id0 - 1];
-                dest = first + ((uint32_t)tile_y - (rmin >> 16)) * (rwh & 0xffffu) + ((uint32_t)tile_x - (rmin & 0xffffu));
+        cp_async_wait<0>();
+        uint32_t ballot[SPT];
+        bool keep[SPT];
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) {
+            const int i = k * NT + tid;
+            const int pos = n - (b + 1) * BATCH + i;
+            keep[k] = false;
+            if (pos >= 0) {
+                const float4 q0 = s_q0[buf][i];
+                const float4 q1 = s_q1[buf][i];
+                const float thr = power_threshold(q1.y);
+                if (q1.y >= ALPHA_MIN_B) {
+                    const ReachCtx rc = make_reach_ctx(q0.x, q0.y, q0.z, q0.w, q1.x, thr, X0, Y0, X1, Y1);
+                    keep[k] = rect_reach(rc, X0, Y0, X1, Y1);
+                }
+                float4 q2 = s_q2[buf][i];
+                uint32_t dest = (uint32_t)idc[k];
+                if (p.deterministic) {
+                    // slot of this instance in the unsorted (Gaussian-major, tile-minor) order
+                    const uint32_t rmin = __float_as_uint(q2.z), rwh = __float_as_uint(q2.w);
+                    const uint32_t first = idc[k] == 0 ? 0u : p.point_offsets[idc[k] - 1];
+                    dest = first + ((uint32_t)tile_y - (rmin >> 16)) * (rwh & 0xffffu) + ((uint32_t)tile_x - (rmin & 0xffffu));
+                }
+                q2.y = thr;
+                q2.z = __uint_as_float((uint32_t)pos);
+                q2.w = __uint_as_float(dest);
+                s_q2[buf][i] = q2;
             }
-            const int slot = warp * 32 + __popc(ballot & lanemask_lt());
-            s_a[buf][slot] = q0;
-            s_b[buf][slot] = make_float4(q1.x, q1.y, thr, __uint_as_float((uint32_t)pos0));
-            s_c[buf][slot] = make_float4(q1.z, q1.w, q2.x, __uint_as_float(dest));
+            ballot[k] = __ballot_sync(FULL_MASK, keep[k]);
+            if (lane == 0) s_cnt[k * NW + warp] = __popc(ballot[k]);
         }
-        if (lane == 0) s_cnt[buf][warp] = __popc(ballot);
         if (NW == 1) __syncwarp(); else __syncthreads();
 
-        for (int w = NW - 1; w >= 0; --w) {
-            const int cnt = s_cnt[buf][w];
-            for (int j = cnt - 1; j >= 0; --j) {
-                const float4 A = s_a[buf][w * 32 + j];
-                const float4 B = s_b[buf][w * 32 + j];
-                const float4 C = s_c[buf][w * 32 + j];
-                const uint32_t lpos = __float_as_uint(B.w);
+        // prefetch the next batch into the other buffer (its previous readers passed the barrier)
+        if (b + 1 < nb) {
+#pragma unroll
+            for (int k = 0; k < SPT; ++k) {
+                if (idn[k] >= 0) {
+                    const int i = k * NT + tid;
+                    const SplatRec* r = p.rec + idn[k];
+                    cp_async16(&s_q0[buf ^ 1][i], &r->q0);
+                    cp_async16(&s_q1[buf ^ 1][i], &r->q1);
+                    cp_async16(&s_q2[buf ^ 1][i], &r->q2);
+                }
+            }
+        }
+        cp_async_commit();
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) {
+            idc[k] = idn[k];
+            const int pos = n - (b + 3) * BATCH + k * NT + tid;
+            idn[k] = (pos >= 0) ? (int)list[pos] : -1;
+        }
+
+        int total = 0;
+        {
+            int base[SPT];
+#pragma unroll
+            for (int k = 0; k < SPT; ++k) base[k] = 0;
+#pragma unroll
+            for (int sgm = 0; sgm < NSEG; ++sgm) {
+                const int c = s_cnt[sgm];
+#pragma unroll
+                for (int k = 0; k < SPT; ++k)
+                    if (sgm < k * NW + warp) base[k] += c;
+                total += c;
+            }
+#pragma unroll
+            for (int k = 0; k < SPT; ++k)
+                if (keep[k]) s_idx[base[k] + __popc(ballot[k] & lt)] = (uint16_t)(k * NT + tid);
+        }
+        if (NW == 1) __syncwarp(); else __syncthreads();
+
+        for (int j0 = ((total - 1) >> 5) << 5; j0 >= 0; j0 -= 32) {
+            // level 2: lane l tests survivor j0+l against each pixel block of this warp
+            uint32_t packed = 0;
+            if (j0 + lane < total) {
+                const uint32_t idx = s_idx[j0 + lane];
+                const float4 A = s_q0[buf][idx];
+                const float4 B = s_q1[buf][idx];
+                const float4 Q = s_q2[buf][idx];
+                const uint32_t lpos = __float_as_uint(Q.z);
+                const ReachCtx rc = make_reach_ctx(A.x, A.y, A.z, A.w, B.x, Q.y, X0, Y0, X1, Y1);
+                uint32_t bits = 0;
+#pragma unroll
+                for (int s = 0; s < PX; ++s) {
+                    const float rx0 = bx0[s % NX], ry0 = by0[s / NX];
+                    if (lpos < blocklast[s] && rect_reach(rc, rx0, ry0, rx0 + 7.0f, ry0 + 3.0f)) bits |= 1u << s;
+                }
+                packed = idx | (bits << 16);
+            }
+            uint32_t m = __ballot_sync(FULL_MASK, (packed >> 16) != 0u);
+            while (m) {
+                const int j = 31 - __clz(m);
+                m &= ~(1u << j);
+                const uint32_t pk = __shfl_sync(FULL_MASK, packed, j);
+                const uint32_t idx = pk & 0xffffu, bj = pk >> 16;
+                const float4 A = s_q0[buf][idx];
+                const float4 B = s_q1[buf][idx];
+                const float4 Q = s_q2[buf][idx];
+                const uint32_t lpos = __float_as_uint(Q.z);
                 float dx[NX], ax[NX], bx[NX], dy[NY], cy[NY];
 #pragma unroll
                 for (int i = 0; i < NX; ++i) {
@@ -166,27 +273,28 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
                 bool any = false;
 #pragma unroll
                 for (int s = 0; s < PX; ++s) {
+                    if (!((bj >> s) & 1u)) continue;          // warp-uniform
                     const int ix = s % NX, iy = s / NX;
                     const float sq = ffma(dx[ix], ax[ix], cy[iy]);
                     const float power = ffma(sq, -0.5f, -fmul(dy[iy], bx[ix]));
                     if (lpos >= lastc[s]) continue;          // behind this pixel's last contributor
-                    if (power > 0.0f || power < B.z) continue;
+                    if (power > 0.0f || power < Q.y) continue;
                     const float G = expf(power);
                     const float alpha = fminf(0.99f, fmul(B.y, G));
                     if (alpha < ALPHA_MIN_B) continue;
                     any = true;
                     const float one_m = 1.0f - alpha;
-                    const float inv = __frcp_rn(one_m);
+                    const float inv = rcp_approx(one_m);
                     T[s] = T[s] * inv;
                     const float wgt = alpha * T[s];
                     acc[0] += wgt * gr[s];
                     acc[1] += wgt * gg[s];
                     acc[2] += wgt * gb[s];
-                    float dL_dalpha = ((C.x - Ar[s]) * gr[s] + (C.y - Ag[s]) * gg[s] + (C.z - Ab[s]) * gb[s]) * T[s];
+                    float dL_dalpha = ((B.z - Ar[s]) * gr[s] + (B.w - Ag[s]) * gg[s] + (Q.x - Ab[s]) * gb[s]) * T[s];
                     dL_dalpha += Tf_bg[s] * inv;
-                    Ar[s] = alpha * C.x + one_m * Ar[s];
-                    Ag[s] = alpha * C.y + one_m * Ag[s];
-                    Ab[s] = alpha * C.z + one_m * Ab[s];
+                    Ar[s] = alpha * B.z + one_m * Ar[s];
+                    Ag[s] = alpha * B.w + one_m * Ag[s];
+                    Ab[s] = alpha * Q.x + one_m * Ab[s];
                     const float gda = G * dL_dalpha;
                     const float u = B.y * gda;
                     const float udx = u * dx[ix], udy = u * dy[iy];
@@ -198,34 +306,28 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
                     acc[8] += gda;
                 }
                 if (!__any_sync(FULL_MASK, any)) continue;
-#pragma unroll
-                for (int i = 0; i < 9; ++i) {
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(FULL_MASK, acc[i], o);
-                }
-                if (lane < 9) {
-                    float v = acc[0];
-#pragma unroll
-                    for (int i = 1; i < 9; ++i) v = (lane == i) ? acc[i] : v;
-                    const uint32_t dest = __float_as_uint(C.w);
+                int which;
+                const float v = reduce9(acc, lane, which);
+                if (which >= 0) {
+                    const uint32_t dest = __float_as_uint(Q.w);
                     if (p.deterministic) {
-                        if (NW == 1) p.partial[(size_t)dest * ACC_STRIDE + lane] = v;
-                        else atomicAdd(&p.partial[(size_t)dest * ACC_STRIDE + lane], v);
+                        if (NW == 1) p.partial[(size_t)dest * ACC_STRIDE + which] = v;
+                        else atomicAdd(&p.partial[(size_t)dest * ACC_STRIDE + which], v);
                     } else {
-                        atomicAdd(&p.accum[(size_t)dest * ACC_STRIDE + lane], v);
+                        atomicAdd(&p.accum[(size_t)dest * ACC_STRIDE + which], v);
                     }
                 }
             }
         }
-        id0 = id1; id1 = id2; pos0 = pos1; pos1 = pos2; q0 = n0; q1 = n1; q2 = n2;
     }
+    cp_async_wait<0>();
 }
 
 template <int NW>
 static int launch_blend_bwd_nw(const BlendBwdParams& p, cudaStream_t stream) {
     const int tiles = p.grid_x * p.grid_y;
     count_launch();
-    blend_bwd_kernel<NW><<<tiles, 32 * NW, 0, stream>>>(p);
+    blend_bwd_kernel<NW, (NW >= 8 ? 1 : BLEND_SPT)><<<tiles, 32 * NW, 0, stream>>>(p);
     return (int)cudaGetLastError();
 }
 

@@ -16,51 +16,27 @@
 //    memory per contributing pixel, forward.cu:355).
 //  * the arithmetic of every decision (power, alpha, T test) mirrors the reference SASS.
 
-#include "kernels.cuh"
+#include "blend_common.cuh"
 
 namespace b200s {
 
 
-constexpr float ALPHA_MIN = 1.0f / 255.0f;
+constexpr float ALPHA_MIN = BLEND_ALPHA_MIN;
 
-// Conservative test: can the Gaussian reach alpha >= 1/255 (with power <= 0) at ANY point of
-// the pixel rectangle [X0,X1]x[Y0,Y1]? Also returns the per-Gaussian power threshold below
-// which alpha < 1/255 is certain. NaNs fall through to "keep".
-__device__ __forceinline__ bool splat_reaches_tile(float x, float y, float a, float b, float c, float op,
-                                                   float X0, float Y0, float X1, float Y1, float& thr) {
-    thr = -logf(255.0f * op) - 1e-4f;           // power < thr  =>  op*exp(power) < 1/255
-    if (op < ALPHA_MIN) return false;           // exp(power) <= 1 for power <= 0
-    const float ex = fminf(fmaxf(x, X0), X1) - x;
-    const float ey = fminf(fmaxf(y, Y0), Y1) - y;
-    if (ex == 0.0f && ey == 0.0f) return true;  // centre inside the tile
-    if (!(a > 0.0f && c > 0.0f && a * c > b * b)) return true;   // not positive definite: no claim
-    const float dx0 = X0 - x, dx1 = X1 - x, dy0 = Y0 - y, dy1 = Y1 - y;
-    float qmin = 3.0e38f;
-    if (ex != 0.0f) {   // nearest vertical edge, minimise over dy
-        const float dy = fminf(fmaxf(__fdividef(-b * ex, c), dy0), dy1);
-        qmin = fminf(qmin, a * ex * ex + 2.0f * b * ex * dy + c * dy * dy);
-    }
-    if (ey != 0.0f) {   // nearest horizontal edge, minimise over dx
-        const float dx = fminf(fmaxf(__fdividef(-b * ey, a), dx0), dx1);
-        qmin = fminf(qmin, a * dx * dx + 2.0f * b * dx * ey + c * ey * ey);
-    }
-    const float mx = fmaxf(fabsf(dx0), fabsf(dx1)), my = fmaxf(fabsf(dy0), fabsf(dy1));
-    const float S = a * mx * mx + 2.0f * fabsf(b) * mx * my + c * my * my;
-    return !(qmin > -2.0f * thr + 4e-6f * S + 1e-4f);
-}
-
-template <int NW>
+template <int NW, int SPT>
 __global__ void __launch_bounds__(32 * NW)
 blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
-    constexpr int PX = 8 / NW;                 // pixels per lane
-    constexpr int NX = PX >= 2 ? 2 : 1;        // distinct pixel columns per lane
-    constexpr int NY = PX >= 2 ? PX / 2 : 1;   // distinct pixel rows per lane
-    constexpr int BATCH = 32 * NW;
+    using WB = WarpBlocks<NW>;
+    constexpr int PX = WB::PX, NX = WB::NX, NY = WB::NY;
+    constexpr int NT = 32 * NW;                // threads per tile
+    constexpr int BATCH = NT * SPT;            // list entries staged per round
+    constexpr int NSEG = NW * SPT;             // 32-entry segments of a batch, in list order
 
-    __shared__ float4 s_a[2][BATCH];           // x, y, conic a, conic b
-    __shared__ float4 s_b[2][BATCH];           // conic c, opacity, power threshold, list pos + 1
-    __shared__ float4 s_c[2][BATCH];           // r, g, b
-    __shared__ int s_cnt[2][NW];
+    __shared__ float4 s_q0[2][BATCH];          // x, y, conic a, conic b
+    __shared__ float4 s_q1[2][BATCH];          // conic c, opacity, r, g
+    __shared__ float4 s_q2[2][BATCH];          // b, power threshold, list pos + 1, -
+    __shared__ uint16_t s_idx[BATCH];          // tile-level survivors of the batch, list order
+    __shared__ int s_cnt[NSEG];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x;
@@ -68,18 +44,21 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     const uint2 range = p.ranges[tile];
     const int n = (int)(range.y - range.x);
 
-    // pixel ownership
-    float pxf[NX], pyf[NY];
+    // pixel ownership: block s = (ix, iy) of this warp, pixel (lane & 7, lane >> 3) inside it
+    float pxf[NX], pyf[NY], bx0[NX], by0[NY];
     int pix_x[NX], pix_y[NY];
-    const int b0 = warp * PX;
 #pragma unroll
     for (int i = 0; i < NX; ++i) {
-        pix_x[i] = tile_x * TILE + (((b0 + i) & 1) * 8) + (lane & 7);
+        const int x0 = tile_x * TILE + WB::col_block(warp, i) * 8;
+        bx0[i] = (float)x0;
+        pix_x[i] = x0 + (lane & 7);
         pxf[i] = (float)pix_x[i];
     }
 #pragma unroll
     for (int i = 0; i < NY; ++i) {
-        pix_y[i] = tile_y * TILE + (((b0 + 2 * i) >> 1) * 4) + (lane >> 3);
+        const int y0 = tile_y * TILE + WB::row_block(warp, i) * 4;
+        by0[i] = (float)y0;
+        pix_y[i] = y0 + (lane >> 3);
         pyf[i] = (float)pix_y[i];
     }
     constexpr uint32_t ALL_DONE = (1u << PX) - 1u;
@@ -99,30 +78,54 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
 
     const int nb = (n + BATCH - 1) / BATCH;
     const uint32_t* list = p.point_list + range.x;
-    // software pipeline: ids two batches ahead, records one batch ahead
-    int id0 = (tid < n) ? (int)list[tid] : -1;
-    int id1 = (BATCH + tid < n) ? (int)list[BATCH + tid] : -1;
-    float4 q0 = make_float4(0, 0, 0, 0), q1 = q0, q2 = q0;
-    if (id0 >= 0) { const SplatRec* r = p.rec + id0; q0 = r->q0; q1 = r->q1; q2 = r->q2; }
+    const uint32_t lt = lanemask_lt();
+
+    // pipeline: ids two batches ahead (registers), records one batch ahead (cp.async -> smem)
+    int idn[SPT];
+#pragma unroll
+    for (int k = 0; k < SPT; ++k) {
+        const int pos = k * NT + tid;
+        if (pos < n) {
+            const SplatRec* r = p.rec + list[pos];
+            cp_async16(&s_q0[0][pos], &r->q0);
+            cp_async16(&s_q1[0][pos], &r->q1);
+            cp_async16(&s_q2[0][pos], &r->q2);
+        }
+    }
+    cp_async_commit();
+#pragma unroll
+    for (int k = 0; k < SPT; ++k) {
+        const int pos = BATCH + k * NT + tid;
+        idn[k] = (pos < n) ? (int)list[pos] : -1;
+    }
 
     for (int b = 0; b < nb; ++b) {
         const int buf = b & 1;
-        const int nxt = (b + 2) * BATCH + tid;
-        const int id2 = (nxt < n) ? (int)list[nxt] : -1;
-        float4 n0 = make_float4(0, 0, 0, 0), n1 = n0, n2 = n0;
-        if (id1 >= 0) { const SplatRec* r = p.rec + id1; n0 = r->q0; n1 = r->q1; n2 = r->q2; }
-
-        float thr;
-        const bool keep = (id0 >= 0) && splat_reaches_tile(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, X0, Y0, X1, Y1, thr);
-        const uint32_t ballot = __ballot_sync(FULL_MASK, keep);
-        if (keep) {
-            const int pos = warp * 32 + __popc(ballot & lanemask_lt());
-            s_a[buf][pos] = q0;
-            s_b[buf][pos] = make_float4(q1.x, q1.y, thr, __uint_as_float((uint32_t)(b * BATCH + tid + 1)));
-            s_c[buf][pos] = make_float4(q1.z, q1.w, q2.x, 0.0f);
+        cp_async_wait<0>();
+        // level 1: every thread tests ITS entries against the tile
+        uint32_t ballot[SPT];
+        bool keep[SPT];
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) {
+            const int i = k * NT + tid;
+            const int pos = b * BATCH + i;
+            keep[k] = false;
+            if (pos < n) {
+                const float4 q0 = s_q0[buf][i];
+                const float4 q1 = s_q1[buf][i];
+                const float thr = power_threshold(q1.y);
+                if (q1.y >= ALPHA_MIN) {
+                    const ReachCtx rc = make_reach_ctx(q0.x, q0.y, q0.z, q0.w, q1.x, thr, X0, Y0, X1, Y1);
+                    keep[k] = rect_reach(rc, X0, Y0, X1, Y1);
+                }
+                float4 q2 = s_q2[buf][i];
+                q2.y = thr;
+                q2.z = __uint_as_float((uint32_t)(pos + 1));
+                s_q2[buf][i] = q2;
+            }
+            ballot[k] = __ballot_sync(FULL_MASK, keep[k]);
+            if (lane == 0) s_cnt[k * NW + warp] = __popc(ballot[k]);
         }
-        if (lane == 0) s_cnt[buf][warp] = __popc(ballot);
-
         bool all_done;
         if (NW == 1) {
             __syncwarp();
@@ -132,11 +135,79 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
         }
         if (all_done) break;
 
-        for (int w = 0; w < NW; ++w) {
-            const int cnt = s_cnt[buf][w];
-            for (int j = 0; j < cnt; ++j) {
-                const float4 A = s_a[buf][w * 32 + j];
-                const float4 B = s_b[buf][w * 32 + j];
+        // prefetch the next batch into the other buffer (its previous readers passed the barrier)
+        if (b + 1 < nb) {
+#pragma unroll
+            for (int k = 0; k < SPT; ++k) {
+                if (idn[k] >= 0) {
+                    const int i = k * NT + tid;
+                    const SplatRec* r = p.rec + idn[k];
+                    cp_async16(&s_q0[buf ^ 1][i], &r->q0);
+                    cp_async16(&s_q1[buf ^ 1][i], &r->q1);
+                    cp_async16(&s_q2[buf ^ 1][i], &r->q2);
+                }
+            }
+        }
+        cp_async_commit();
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) {
+            const int pos = (b + 2) * BATCH + k * NT + tid;
+            idn[k] = (pos < n) ? (int)list[pos] : -1;
+        }
+
+        // compact the survivors' indices in list order
+        int total = 0;
+        {
+            int base[SPT];
+#pragma unroll
+            for (int k = 0; k < SPT; ++k) base[k] = 0;
+#pragma unroll
+            for (int sgm = 0; sgm < NSEG; ++sgm) {
+                const int c = s_cnt[sgm];
+#pragma unroll
+                for (int k = 0; k < SPT; ++k)
+                    if (sgm < k * NW + warp) base[k] += c;
+                total += c;
+            }
+#pragma unroll
+            for (int k = 0; k < SPT; ++k)
+                if (keep[k]) s_idx[base[k] + __popc(ballot[k] & lt)] = (uint16_t)(k * NT + tid);
+        }
+        if (NW == 1) __syncwarp(); else __syncthreads();
+
+        // pixel blocks whose 32 pixels are all finished take no more entries
+        uint32_t blockdone = 0;
+#pragma unroll
+        for (int s = 0; s < PX; ++s)
+            if (__all_sync(FULL_MASK, (done >> s) & 1u)) blockdone |= 1u << s;
+
+        for (int j0 = 0; j0 < total; j0 += 32) {
+            // level 2: lane l tests survivor j0+l against each pixel block of this warp
+            uint32_t packed = 0;
+            if (j0 + lane < total) {
+                const uint32_t idx = s_idx[j0 + lane];
+                const float4 A = s_q0[buf][idx];
+                const float4 B = s_q1[buf][idx];
+                const float thr = s_q2[buf][idx].y;
+                const ReachCtx rc = make_reach_ctx(A.x, A.y, A.z, A.w, B.x, thr, X0, Y0, X1, Y1);
+                uint32_t bits = 0;
+#pragma unroll
+                for (int s = 0; s < PX; ++s) {
+                    const float rx0 = bx0[s % NX], ry0 = by0[s / NX];
+                    if (rect_reach(rc, rx0, ry0, rx0 + 7.0f, ry0 + 3.0f)) bits |= 1u << s;
+                }
+                bits &= ~blockdone;
+                packed = idx | (bits << 16);
+            }
+            uint32_t m = __ballot_sync(FULL_MASK, (packed >> 16) != 0u);
+            while (m) {
+                const int j = __ffs(m) - 1;
+                m &= m - 1;
+                const uint32_t pk = __shfl_sync(FULL_MASK, packed, j);
+                const uint32_t idx = pk & 0xffffu, bj = pk >> 16;
+                const float4 A = s_q0[buf][idx];
+                const float4 B = s_q1[buf][idx];
+                const float4 Q = s_q2[buf][idx];
                 float dx[NX], ax[NX], bx[NX], dy[NY], cy[NY];
 #pragma unroll
                 for (int i = 0; i < NX; ++i) {
@@ -151,26 +222,26 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
                 }
 #pragma unroll
                 for (int s = 0; s < PX; ++s) {
+                    if (!((bj >> s) & 1u)) continue;          // warp-uniform
                     const int ix = s % NX, iy = s / NX;
                     const float sq = ffma(dx[ix], ax[ix], cy[iy]);
                     const float power = ffma(sq, -0.5f, -fmul(dy[iy], bx[ix]));
                     if ((done >> s) & 1u) continue;
-                    if (power > 0.0f || power < B.z) continue;
+                    if (power > 0.0f || power < Q.y) continue;
                     const float alpha = fminf(0.99f, fmul(B.y, expf(power)));
                     if (alpha < ALPHA_MIN) continue;
                     const float test_T = fmul(T[s], fsub(1.0f, alpha));
                     if (test_T < 0.0001f) { done |= 1u << s; continue; }
-                    const float4 C = s_c[buf][w * 32 + j];
-                    Cr[s] = ffma(T[s], fmul(alpha, C.x), Cr[s]);
-                    Cg[s] = ffma(T[s], fmul(alpha, C.y), Cg[s]);
-                    Cb[s] = ffma(T[s], fmul(alpha, C.z), Cb[s]);
+                    Cr[s] = ffma(T[s], fmul(alpha, B.z), Cr[s]);
+                    Cg[s] = ffma(T[s], fmul(alpha, B.w), Cg[s]);
+                    Cb[s] = ffma(T[s], fmul(alpha, Q.x), Cb[s]);
                     T[s] = test_T;
-                    last[s] = __float_as_uint(B.w);
+                    last[s] = __float_as_uint(Q.z);
                 }
             }
         }
-        id0 = id1; id1 = id2; q0 = n0; q1 = n1; q2 = n2;
     }
+    cp_async_wait<0>();
 
     // epilogue
     const float bg0 = p.background[0], bg1 = p.background[1], bg2 = p.background[2];
@@ -244,7 +315,7 @@ template <int NW>
 static int launch_blend_fwd_nw(const BlendFwdParams& p, cudaStream_t stream) {
     const int tiles = p.grid_x * p.grid_y;
     count_launch();
-    blend_fwd_kernel<NW><<<tiles, 32 * NW, 0, stream>>>(p);
+    blend_fwd_kernel<NW, (NW >= 8 ? 1 : BLEND_SPT)><<<tiles, 32 * NW, 0, stream>>>(p);
     return (int)cudaGetLastError();
 }
 
