@@ -110,6 +110,7 @@ int check_forward_args(const B200sForwardArgs* a) {
     if (has_sr == (a->cov3D_precomp != nullptr)) return B200S_E_BADARG;
     if (a->shs && a->M <= 0) return B200S_E_BADARG;
     if (a->W > 65535 * TILE || a->H > 65535 * TILE) return B200S_E_UNSUPPORTED;
+    if (a->P >= (1 << 30)) return B200S_E_UNSUPPORTED;   // packed look-back word of scan_compact
     if (!a->geom_ws || !a->img_ws) return B200S_E_BADARG;
     if (a->geom_bytes < b200s_geometry_workspace_size(a->P)) return B200S_E_WORKSPACE;
     if (a->img_bytes < b200s_image_workspace_size(a->W, a->H)) return B200S_E_WORKSPACE;
@@ -173,7 +174,7 @@ int b200s_forward_preprocess(const B200sForwardArgs* a, b200s_stream_t stream_) 
     B200S_CUDA_OK(cudaMemsetAsync(g.header, 0, sizeof(B200sHeader), stream));
     B200S_CUDA_OK(cudaMemsetAsync(g.counters, 0, 64 * sizeof(uint32_t), stream));
     if (a->P == 0) return 0;
-    B200S_CUDA_OK(cudaMemsetAsync(g.scan_status, 0, 4 * ((size_t)(a->P + SCAN_TILE - 1) / SCAN_TILE + 1), stream));
+    B200S_CUDA_OK(cudaMemsetAsync((char*)a->geom_ws + g.zero_off, 0, g.zero_bytes, stream));
     PreprocessParams p;
     p.P = a->P; p.D = a->D; p.M = a->M; p.W = a->W; p.H = a->H;
     p.grid_x = d.gx; p.grid_y = d.gy;
@@ -182,7 +183,8 @@ int b200s_forward_preprocess(const B200sForwardArgs* a, b200s_stream_t stream_) 
     p.means3D = a->means3D; p.shs = a->shs; p.colors_precomp = a->colors_precomp; p.opacities = a->opacities;
     p.scales = a->scales; p.rotations = a->rotations; p.cov3D_precomp = a->cov3D_precomp;
     p.viewmatrix = a->viewmatrix; p.projmatrix = a->projmatrix; p.campos = a->campos;
-    p.radii = a->radii; p.rec = g.rec; p.tiles_touched = g.tiles_touched; p.clamped = g.clamped;
+    p.radii = a->radii; p.rec = g.rec; p.tiles_touched = g.tiles_touched; p.depth_bits = g.depth_bits;
+    p.clamped = g.clamped;
     p.header = g.header; p.counters = g.counters;
     {
         ProfScope ps(B200S_STAGE_PREPROCESS, stream);
@@ -190,13 +192,7 @@ int b200s_forward_preprocess(const B200sForwardArgs* a, b200s_stream_t stream_) 
     }
     if (rc) return rc;
     B200S_AFTER_LAUNCH(stream, a->debug);
-    {
-        ProfScope ps(B200S_STAGE_SCAN, stream);
-        rc = launch_scan(g.tiles_touched, g.point_offsets, a->P, g.scan_status, g.counters, g.header, stream);
-    }
-    if (rc) return rc;
-    B200S_AFTER_LAUNCH(stream, a->debug);
-    return 0;
+    return launch_scan_and_depth_sort(a->P, g, a->debug != 0, stream);
 }
 
 int b200s_forward_render(const B200sForwardArgs* a, b200s_stream_t stream_) {
@@ -222,8 +218,10 @@ int b200s_forward_render(const B200sForwardArgs* a, b200s_stream_t stream_) {
     // stage 2 may be re-run with a larger workspace after an overflow: reset its device state
     B200S_CUDA_OK(cudaMemsetAsync(&g.header->overflow, 0, sizeof(uint32_t), stream));
     B200S_CUDA_OK(cudaMemsetAsync(g.counters + CTR_SORT_TICKET0, 0, SORT_MAX_PASSES * sizeof(uint32_t), stream));
-    rc = launch_binning(a->P, g.rec, g.point_offsets, bw, a->bin_capacity, a->bin_capacity, d.gx, d.tiles,
-                        im.ranges, g.header, g.counters, &final_buf, a->debug != 0, stream);
+    B200S_CUDA_OK(cudaMemsetAsync(g.counters + CTR_EXPAND_TICKET, 0, sizeof(uint32_t), stream));
+    B200S_CUDA_OK(cudaMemsetAsync(g.exp_status, 0, 4 * ((size_t)(a->P + EXP_TILE - 1) / EXP_TILE + 1), stream));
+    rc = launch_binning(a->P, g, bw, a->bin_capacity, a->bin_capacity, d.gx, d.tiles, im.ranges, &final_buf,
+                        a->debug != 0, stream);
     if (rc) return rc;
     BlendFwdParams b;
     b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;

@@ -41,14 +41,37 @@ constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
+// Radix sort geometry (see binning.cu).
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
+constexpr int SORT_MAX_PASSES = 4;    // onesweep passes over the tile bits (<= 32 bits of tile id)
+constexpr int DEPTH_PASSES = 4;       // onesweep passes over the 32 depth bits
+
+// Expansion geometry: one block turns EXP_TILE depth-sorted Gaussians into their instances.
+constexpr int EXP_THREADS = 256;
+constexpr int EXP_ITEMS = 4;
+constexpr int EXP_TILE = EXP_THREADS * EXP_ITEMS;
+constexpr int EXP_OUT_TILE = EXP_THREADS * 8;   // instances emitted per expansion block
+
 struct GeomWS {
     B200sHeader* header;      // 64 B
     uint32_t* counters;       // 64 x u32 device tickets (scan ticket, sort tickets, ...)
     SplatRec* rec;            // [P]
     uint32_t* tiles_touched;  // [P]
-    uint32_t* point_offsets;  // [P] inclusive prefix sum of tiles_touched
+    uint32_t* point_offsets;  // [P] inclusive prefix sum of tiles_touched (Gaussian-index order)
     uint8_t* clamped;         // [P] bit c set when SH colour channel c was clamped at 0
-    uint32_t* scan_status;    // [ceil(P / SCAN_TILE) + 1] decoupled look-back words
+    uint32_t* depth_bits;     // [P] view-space depth of visible Gaussians (float bits)
+    uint32_t* vis_keys[2];    // [P] depth bits of the compacted visible Gaussians (ping-pong)
+    uint32_t* vis_ids[2];     // [P] their Gaussian ids; after the depth sort: front-to-back order
+    unsigned long long* scan_status;   // [ceil(P / SCAN_TILE) + 1] decoupled look-back words
+    uint32_t* depth_hist;     // [DEPTH_PASSES][SORT_RADIX]
+    uint32_t* depth_lookback; // [DEPTH_PASSES][ceil(P / SORT_TILE)][SORT_RADIX]
+    uint32_t* exp_status;     // [ceil(P / EXP_TILE) + 1] look-back words of the expansion
+    size_t zero_off, zero_bytes;   // scan_status..exp_status are contiguous: cleared every call
+    int64_t depth_tiles;
     size_t bytes;
 };
 
@@ -63,7 +86,18 @@ inline GeomWS carve_geom(void* base, int64_t P) {
     g.tiles_touched = (uint32_t*)take(4 * (size_t)P);
     g.point_offsets = (uint32_t*)take(4 * (size_t)P);
     g.clamped = (uint8_t*)take((size_t)P);
-    g.scan_status = (uint32_t*)take(4 * ((size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1));
+    g.depth_bits = (uint32_t*)take(4 * (size_t)P);
+    for (int i = 0; i < 2; ++i) {
+        g.vis_keys[i] = (uint32_t*)take(4 * (size_t)P);
+        g.vis_ids[i] = (uint32_t*)take(4 * (size_t)P);
+    }
+    g.depth_tiles = (P + SORT_TILE - 1) / SORT_TILE;
+    g.zero_off = off;
+    g.scan_status = (unsigned long long*)take(8 * ((size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1));
+    g.depth_hist = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * SORT_RADIX);
+    g.depth_lookback = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * g.depth_tiles * SORT_RADIX);
+    g.exp_status = (uint32_t*)take(4 * ((size_t)(P + EXP_TILE - 1) / EXP_TILE + 1));
+    g.zero_bytes = off - g.zero_off;
     g.bytes = off;
     return g;
 }
@@ -91,19 +125,12 @@ inline ImgWS carve_img(void* base, int W, int H) {
     return s;
 }
 
-// Radix sort geometry (see binning.cu).
-constexpr int SORT_RADIX_BITS = 8;
-constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
-constexpr int SORT_MAX_PASSES = 4;    // onesweep passes over the tile bits (<= 32 bits of tile id)
-
 struct BinWS {
-    uint64_t* keys[2];     // [capacity] ping-pong
-    uint32_t* vals[2];     // [capacity]
+    uint32_t* keys[2];     // [capacity] tile id of every instance (ping-pong)
+    uint32_t* vals[2];     // [capacity] Gaussian id of every instance
     uint32_t* hist;        // [SORT_MAX_PASSES][SORT_RADIX] digit histograms -> exclusive bases
     uint32_t* lookback;    // [SORT_MAX_PASSES][sort_tiles][SORT_RADIX]
+    uint32_t* block_first; // [capacity / EXP_OUT_TILE + 2] first Gaussian of every expansion block
     size_t zero_bytes;     // hist+lookback are contiguous: bytes to clear before a sort
     int64_t sort_tiles;
     size_t bytes;
@@ -116,14 +143,15 @@ inline BinWS carve_bin(void* base, int64_t capacity) {
     auto take = [&](size_t n) { char* p = b + off; off = align_up(off + n); return p; };
     if (capacity < 1) capacity = 1;
     s.sort_tiles = (capacity + SORT_TILE - 1) / SORT_TILE;
-    s.keys[0] = (uint64_t*)take(8 * (size_t)capacity);
-    s.keys[1] = (uint64_t*)take(8 * (size_t)capacity);
+    s.keys[0] = (uint32_t*)take(4 * (size_t)capacity);
+    s.keys[1] = (uint32_t*)take(4 * (size_t)capacity);
     s.vals[0] = (uint32_t*)take(4 * (size_t)capacity);
     s.vals[1] = (uint32_t*)take(4 * (size_t)capacity);
     size_t z0 = off;
     s.hist = (uint32_t*)take(4 * (size_t)SORT_MAX_PASSES * SORT_RADIX);
     s.lookback = (uint32_t*)take(4 * (size_t)SORT_MAX_PASSES * s.sort_tiles * SORT_RADIX);
     s.zero_bytes = off - z0;
+    s.block_first = (uint32_t*)take(4 * ((size_t)capacity / EXP_OUT_TILE + 2));
     s.bytes = off;
     return s;
 }
@@ -151,8 +179,8 @@ inline BwdWS carve_bwd(void* base, int64_t P, int64_t R) {
 }
 
 // Device-side counters (GeomWS::counters) -------------------------------------------
-enum { CTR_SCAN_TICKET = 0, CTR_SORT_TICKET0 = 1 /* ..+SORT_MAX_PASSES */, CTR_VISIBLE = 16,
-       CTR_TILE_TICKET = 17, CTR_TILE_TICKET_BWD = 18 };
+enum { CTR_SCAN_TICKET = 0, CTR_SORT_TICKET0 = 1 /* ..+SORT_MAX_PASSES */, CTR_DEPTH_TICKET0 = 8 /* ..+DEPTH_PASSES */,
+       CTR_EXPAND_TICKET = 15, CTR_VISIBLE = 16 };
 
 // Device error bits (B200sHeader::error)
 enum { ERR_LOOKBACK_TIMEOUT = 1u, ERR_PREFILTERED = 2u };

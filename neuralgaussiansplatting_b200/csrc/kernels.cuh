@@ -22,6 +22,7 @@ struct PreprocessParams {
     int* radii;
     SplatRec* rec;
     uint32_t* tiles_touched;
+    uint32_t* depth_bits;
     uint8_t* clamped;
     B200sHeader* header;
     uint32_t* counters;
@@ -97,12 +98,10 @@ int launch_count_pairs(const BlendFwdParams& p, unsigned long long* counts, cuda
 
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
-int launch_scan(const uint32_t* in, uint32_t* out, int P, uint32_t* status, uint32_t* counters,
-                B200sHeader* header, cudaStream_t stream);
+int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t stream);
 int sort_num_passes(int tiles);
-int launch_binning(int P, const SplatRec* rec, const uint32_t* offsets, const BinWS& bw, int64_t capacity,
-                   int64_t n_hint, int grid_x, int tiles, uint2* ranges, B200sHeader* header,
-                   uint32_t* counters, int* final_buf, bool debug, cudaStream_t stream);
+int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, int64_t n_hint, int grid_x,
+                   int tiles, uint2* ranges, int* final_buf, bool debug, cudaStream_t stream);
 int launch_blend_fwd(const BlendFwdParams& p, int nw, cudaStream_t stream);
 int launch_blend_bwd(const BlendBwdParams& p, int nw, cudaStream_t stream);
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream);

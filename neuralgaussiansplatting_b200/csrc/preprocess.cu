@@ -213,10 +213,10 @@ preprocess_fwd_kernel(const __grid_constant__ PreprocessParams p) {
                                __uint_as_float((uint32_t)(rect.x1 - rect.x0) |
                                                ((uint32_t)(rect.y1 - rect.y0) << 16)));
             p.rec[idx] = r;
+            p.depth_bits[idx] = __float_as_uint(depth);
             p.clamped[idx] = (uint8_t)clamp_bits;
         }
     }
-    if (lane == 0 && vis_mask != 0) atomicAdd(&p.counters[CTR_VISIBLE], (uint32_t)__popc(vis_mask));
 }
 
 // K10 — markVisible / checkFrustum (rasterizer_impl.cu:54-66,141-153)
