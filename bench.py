@@ -89,14 +89,16 @@ def barrier_sync(world, dev):
     torch.cuda.synchronize(dev)
 
 
-def timed_region(fn, steps, world, dev, sampler=None):
+def timed_region(fn, steps, world, dev, sampler=None, finalize=None):
     """EXACTLY `steps` calls of fn(step) between barrier+synchronize, CUDA events on the current stream,
-    MAX over ranks."""
+    MAX over ranks. `finalize` (pipelined loops: last all-reduce wait, last loss read-back) runs INSIDE the region."""
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier_sync(world, dev)
     e0.record()
     for s in range(steps):
         fn(s)
+    if finalize is not None:
+        finalize()
     e1.record()
     barrier_sync(world, dev)
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
@@ -202,28 +204,57 @@ def run_ours(args, rank, local_rank, world, dev):
     reducer = parallel.GradientAllReduce() if world > 1 else None
     GRAD_KEYS = {"means3D": 3, "opacities": 2, "shs": 5, "scales": 6, "rotations": 7}   # slots of the 8-tuple
 
-    def step_resident(s):
+    overlap = args.allreduce == "overlap"
+
+    def reduce_step(grads):
+        if reducer is None:
+            return
+        if overlap:
+            reducer.wait()          # the reduce of the PREVIOUS view ran while this view was rasterized
+            reducer.start(grads)
+        else:
+            reducer.start(grads)
+            reducer.wait()
+
+    def reduce_finalize():
+        if reducer is not None:
+            reducer.wait()
+
+    def step_resident(s, collective=True):
         v = w.view_of(s)
         fa = w.fwd_args(v)
         out = _C.rasterize_gaussians(*fa)
         g = _C.rasterize_gaussians_backward(fa[0], fa[1], out[2], fa[2], fa[4], fa[5], fa[6], fa[7], fa[8], fa[9],
                                             fa[10], fa[11], w.dL[v], fa[14], fa[15], fa[16], out[3], out[0], out[4],
                                             out[5], False)
-        if reducer is not None:
-            reducer.start({k: g[i] for k, i in GRAD_KEYS.items()})
-            reducer.wait()
+        if collective:
+            reduce_step({k: g[i] for k, i in GRAD_KEYS.items()})
         return g
 
-    # ---- e2e: the call a user makes (nn.Module + autograd), host inputs copied inside the timed region
+    # ---- e2e: the call a user makes (nn.Module + autograd). Every step's host inputs (camera block + ground-truth
+    # image, pinned) are copied H2D and its loss is read back D2H inside the timed region; the copies go through
+    # the package's view pipeline (pipeline.ViewPrefetcher / DeferredScalar): view k+1 uploads while view k
+    # rasterizes and the loss is consumed one step late, as a training loop that logs its loss would do.
+    from neuralgaussiansplatting_b200.pipeline import DeferredScalar, ViewPrefetcher
     params = {k: w.scene[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "scales", "rotations", "shs")}
-    cam_dev = torch.empty(35, device=dev)
-    gt_dev = torch.empty(3, cfg.height, cfg.width, device=dev)
-    loss_host = torch.zeros(1).pin_memory()
+    pf = ViewPrefetcher(dev, {"cam": ((35,), torch.float32), "gt": ((3, cfg.height, cfg.width), torch.float32)})
+    losses = DeferredScalar(lag=1)
+    state = {"steps": 0, "submitted": 0, "read": 0}
+
+    def e2e_begin(steps):
+        state.update(steps=steps, submitted=0, read=0)
+
+    def host_view(s):
+        v = w.view_of(s)
+        return {"cam": w.cam_host[v], "gt": w.gt_host[v]}
 
     def step_e2e(s):
-        v = w.view_of(s)
-        cam_dev.copy_(w.cam_host[v], non_blocking=True)
-        gt_dev.copy_(w.gt_host[v], non_blocking=True)
+        if state["submitted"] == 0:                       # first view of the region: nothing was prefetched
+            pf.submit(host_view(s)); state["submitted"] += 1
+        buf = pf.acquire()
+        if state["submitted"] < state["steps"]:           # upload the next view behind this one's rasterization
+            pf.submit(host_view(s + 1)); state["submitted"] += 1
+        cam_dev, gt_dev = buf["cam"], buf["gt"]
         settings = GaussianRasterizationSettings(cfg.height, cfg.width, w.tan[0], w.tan[1], w.bg, 1.0,
                                                  cam_dev[0:16].view(4, 4), cam_dev[16:32].view(4, 4), 3,
                                                  cam_dev[32:35], False, False)
@@ -234,23 +265,33 @@ def run_ours(args, rank, local_rank, world, dev):
                                                   cov3D_precomp=None)
         loss = (img - gt_dev).abs().mean()
         loss.backward()
-        if reducer is not None:
-            reducer.start({k: p.grad for k, p in params.items()})
-            reducer.wait()
-        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()       # the step's result is on the host
+        reduce_step({k: p.grad for k, p in params.items()})
+        if losses.push(loss) is not None:                 # loss of the previous step is now on the host
+            state["read"] += 1
         for p in params.values():
             p.grad = None
 
+    def e2e_finalize():
+        reduce_finalize()
+        pf.release()
+        state["read"] += len(losses.drain())
+        torch.cuda.current_stream().synchronize()
+        assert state["read"] == state["steps"] and state["submitted"] == state["steps"], state
+
     for s in range(args.warmup):
         step_resident(s)
+    reduce_finalize()
     launches0 = lib.b200s_launch_count()
     with ClockSampler(local_rank) as clk:
-        ms_total = timed_region(step_resident, args.steps, world, dev)
+        ms_total = timed_region(step_resident, args.steps, world, dev, finalize=reduce_finalize)
     launches = int(lib.b200s_launch_count() - launches0)
-    for s in range(max(args.warmup, 3)):
+    nw = max(args.warmup, 3)
+    e2e_begin(nw)
+    for s in range(nw):
         step_e2e(s)
-    ms_e2e = timed_region(step_e2e, args.steps, world, dev)
+    e2e_finalize()
+    e2e_begin(args.steps)
+    ms_e2e = timed_region(step_e2e, args.steps, world, dev, finalize=e2e_finalize)
 
     out = {
         "metric": METRIC, "value": round(world * args.steps / (ms_total * 1e-3), 3), "unit": UNIT,
@@ -260,18 +301,23 @@ def run_ours(args, rank, local_rank, world, dev):
         "config": {"workload": f"{cfg.name}: {w.P} Gaussians SH3, {cfg.width}x{cfg.height}, fwd+bwd, 1 view/step/GPU "
                                f"cycling {w.nviews} orbit views" + (", + NCCL SUM all-reduce of 59 floats/Gaussian"
                                                                      if world > 1 else ""),
+                   "allreduce": ("none (1 GPU)" if world == 1 else
+                                 "overlap: the reduce of view k runs on the NCCL stream while view k+1 is rasterized "
+                                 "(north_star); every reduce completes inside the timed region" if overlap else
+                                 "blocking: reduce exposed after every view"),
                    "parallelism": f"view-parallel x{world}, Gaussians replicated",
                    "l2": "inputs (708 MB of Gaussian parameters) exceed the 126 MB L2; no explicit flush",
                    "blend_mode": "strict (expf, bit-exact n_contrib)"},
         "e2e": {"value": round(world * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
                 "ms_per_step": round(ms_e2e / args.steps, 4), "h2d_bytes_per_step": w.h2d_bytes,
                 "d2h_bytes_per_step": w.d2h_bytes,
-                "api": "GaussianRasterizer(nn.Module)+autograd, L1 loss vs host ground truth"},
+                "api": "GaussianRasterizer(nn.Module)+autograd, L1 loss vs host ground truth; per-step H2D through "
+                       "pipeline.ViewPrefetcher (next view uploads behind the current one), loss read one step late"},
         "gpu_launches": launches,
         "clocks": clk.summary(),
     }
     if rank == 0:
-        out.update(roofline_pass(args, w, lib, _C, step_resident))
+        out.update(roofline_pass(args, w, lib, _C, lambda s: step_resident(s, collective=False)))
         if not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(w)
     return out
@@ -380,7 +426,24 @@ def run_reference(args, rank, local_rank, world, dev):
     cfg = w.cfg
     ref = refbind.RefDGR()
     reducer = parallel.GradientAllReduce() if world > 1 else None
+    overlap = args.allreduce == "overlap"      # same communication mode as our arm: the all-reduce is ours in both
     s_ = w.scene
+
+    def reduce_step(g):
+        if reducer is None:
+            return
+        grads = {"means3D": g["means3D"], "opacities": g["opacity"], "shs": g["sh"], "scales": g["scales"],
+                 "rotations": g["rotations"]}
+        if overlap:
+            reducer.wait()
+            reducer.start(grads)
+        else:
+            reducer.start(grads)
+            reducer.wait()
+
+    def reduce_finalize():
+        if reducer is not None:
+            reducer.wait()
 
     def kw_of(v, view=None, proj=None, campos=None):
         c = w.cams[v]
@@ -395,10 +458,7 @@ def run_reference(args, rank, local_rank, world, dev):
     def fwd_bwd(kw, dL):
         R, color, radii = ref.forward(sync=False, **kw)
         g = ref.backward(radii=radii, dL_dpix=dL, sync=False, **{k: kw[k] for k in BK})
-        if reducer is not None:
-            reducer.start({"means3D": g["means3D"], "opacities": g["opacity"], "shs": g["sh"], "scales": g["scales"],
-                           "rotations": g["rotations"]})
-            reducer.wait()
+        reduce_step(g)
         return color
 
     def step_resident(s):
@@ -419,20 +479,19 @@ def run_reference(args, rank, local_rank, world, dev):
         loss = diff.abs().mean()
         dL = torch.sign(diff) / diff.numel()                 # d(L1 mean)/d(color), what autograd would hand back
         g = ref.backward(radii=radii, dL_dpix=dL, sync=False, **{k: kw[k] for k in BK})
-        if reducer is not None:
-            reducer.start({"means3D": g["means3D"], "opacities": g["opacity"], "shs": g["sh"], "scales": g["scales"],
-                           "rotations": g["rotations"]})
-            reducer.wait()
+        reduce_step(g)
         loss_host.copy_(loss.reshape(1), non_blocking=True)
         torch.cuda.current_stream().synchronize()
 
     for s in range(args.warmup):
         step_resident(s)
+    reduce_finalize()
     with ClockSampler(local_rank) as clk:
-        ms_total = timed_region(step_resident, args.steps, world, dev)
+        ms_total = timed_region(step_resident, args.steps, world, dev, finalize=reduce_finalize)
     for s in range(max(args.warmup, 3)):
         step_e2e(s)
-    ms_e2e = timed_region(step_e2e, args.steps, world, dev)
+    reduce_finalize()
+    ms_e2e = timed_region(step_e2e, args.steps, world, dev, finalize=reduce_finalize)
     ref.close()
     value = round(world * args.steps / (ms_total * 1e-3), 3)
     return {
@@ -442,6 +501,10 @@ def run_reference(args, rank, local_rank, world, dev):
         "config": {"workload": f"{cfg.name}: {w.P} Gaussians SH3, {cfg.width}x{cfg.height}, fwd+bwd, 1 view/step/GPU "
                                f"cycling {w.nviews} orbit views" + (", + NCCL SUM all-reduce of 59 floats/Gaussian"
                                                                      if world > 1 else ""),
+                   "allreduce": ("none (1 GPU)" if world == 1 else
+                                 "overlap: the reduce of view k runs on the NCCL stream while view k+1 is rasterized "
+                                 "(north_star); every reduce completes inside the timed region" if overlap else
+                                 "blocking: reduce exposed after every view"),
                    "parallelism": f"view-parallel x{world}, Gaussians replicated",
                    "what": "unmodified reference diff-gaussian-rasterization kernels compiled for sm_100 "
                            "(oracle/_ref), same GPU, same inputs; the reference has no CPU implementation of this "
@@ -465,6 +528,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--allreduce", default="overlap", choices=["overlap", "blocking"],
+                    help="N>1: overlap the gradient all-reduce of view k with the rasterization of view k+1")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank, local_rank, world = env_world()
@@ -476,7 +541,8 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     try:
         res = run_reference(args, rank, local_rank, world, dev) if args.impl == "reference" else \
             run_ours(args, rank, local_rank, world, dev)

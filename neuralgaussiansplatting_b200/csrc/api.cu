@@ -83,7 +83,7 @@ int env_int(const char* name, int dflt) {
     if (!v || !*v) return dflt;
     return atoi(v);
 }
-int blend_fwd_warps() { static int v = env_int("B200S_BLEND_FWD_WARPS", 4); return v; }
+int blend_fwd_warps() { static int v = env_int("B200S_BLEND_FWD_WARPS", 2); return v; }
 int blend_bwd_warps() { static int v = env_int("B200S_BLEND_BWD_WARPS", 4); return v; }
 
 struct Dims { int gx, gy, tiles; float focal_x, focal_y; };

@@ -28,6 +28,7 @@
 //  * N (num_rendered) is read from device memory by every kernel: no host round trip is
 //    needed between the stages (the reference blocks on a 4-byte D2H, rasterizer_impl.cu:281).
 
+#include <cstdlib>
 #include "kernels.cuh"
 
 namespace b200s {
@@ -72,6 +73,79 @@ __device__ __forceinline__ unsigned long long wait_status64(const unsigned long 
         v = ld_volatile_u64(p);
     }
     return v;
+}
+
+
+// Warp-cooperative decoupled look-back for a scan with ONE value per tile: the 32 lanes read the
+// 32 predecessors' status words at once and consume them up to the first inclusive word / first
+// word not yet published. Returns the exclusive prefix of `tile` (same value in every lane).
+// Packed u64 words (two fields) are summed as they are: the caller guarantees no carry between fields.
+template <typename T>
+__device__ __forceinline__ T warp_lookback(const T* status, int64_t tile, B200sHeader* header) {
+    const int lane = threadIdx.x & 31;
+    T excl = 0;
+    int64_t t = tile - 1;
+    int spins = 0;
+    while (t >= 0) {
+        const int64_t idx = t - lane;
+        T w = (T)FLAG_INCL;                       // virtual inclusive zero in front of tile 0
+        if (idx >= 0) {
+            if (sizeof(T) == 8) w = (T)ld_volatile_u64(reinterpret_cast<const unsigned long long*>(status + idx));
+            else w = (T)ld_volatile_u32(reinterpret_cast<const uint32_t*>(status + idx));
+        }
+        const uint32_t flag = (uint32_t)(w & (T)3);
+        const uint32_t nr = __ballot_sync(FULL_MASK, flag == 0u);
+        const uint32_t inc = __ballot_sync(FULL_MASK, flag == FLAG_INCL);
+        const int first_nr = nr ? __ffs(nr) - 1 : 32;
+        const int first_inc = inc ? __ffs(inc) - 1 : 32;
+        const bool done = first_inc < first_nr;
+        const int take = done ? first_inc + 1 : first_nr;
+        T v = lane < take ? (w >> 2) : (T)0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL_MASK, v, o);
+        excl += v;
+        if (done) break;
+        t -= take;
+        if (take == 0) {
+            if (++spins > SPIN_LIMIT) {
+                if (lane == 0) atomicOr(&header->error, (uint32_t)ERR_LOOKBACK_TIMEOUT);
+                break;
+            }
+            __nanosleep(20);
+        }
+    }
+    return excl;
+}
+
+// Per-thread look-back (one chain per radix digit) with LB independent loads in flight per step.
+constexpr int LB_DEPTH = 8;
+__device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t stride, int64_t tile, B200sHeader* header) {
+    uint32_t excl = 0;
+    int64_t t = tile - 1;
+    int spins = 0;
+    while (t >= 0) {
+        uint32_t w[LB_DEPTH];
+#pragma unroll
+        for (int i = 0; i < LB_DEPTH; ++i)
+            w[i] = (t - i >= 0) ? ld_volatile_u32(col + (size_t)(t - i) * stride) : FLAG_INCL;
+        bool done = false, stop = false;
+        int take = 0;
+#pragma unroll
+        for (int i = 0; i < LB_DEPTH; ++i) {
+            if (!done && !stop) {
+                const uint32_t f = w[i] & 3u;
+                if (f == 0u) stop = true;
+                else { excl += w[i] >> 2; ++take; if (f == FLAG_INCL) done = true; }
+            }
+        }
+        if (done) break;
+        t -= take;
+        if (take == 0) {
+            if (++spins > SPIN_LIMIT) { atomicOr(&header->error, (uint32_t)ERR_LOOKBACK_TIMEOUT); break; }
+            __nanosleep(20);
+        }
+    }
+    return excl;
 }
 
 // ---------------------------------------------------------------------- scan + compaction
@@ -130,24 +204,16 @@ scan_compact_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict_
         if (w < warp) warp_excl += t;
         total += t;
     }
-    if (tid == 0) {
-        // both halves stay below 2^30 / 2^31, so (x << 2) of the packed word carries no overflow
-        // between the fields as long as the tile sum fits 30 bits (checked by the host: capacity < 2^30)
+    if (warp == 0) {
+        // packed word << 2: the tile sum (< 2^32) moves to bits [2,34), the visible count (< 2^30,
+        // checked by the host) to [34,64)
+        if (lane == 0) st_volatile_u64(&status[tile], (total << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
         unsigned long long excl = 0;
-        if (tile == 0) {
-            st_volatile_u64(&status[0], (total << 2) | FLAG_INCL);
-        } else {
-            st_volatile_u64(&status[tile], (total << 2) | FLAG_AGG);
-            int64_t t = (int64_t)tile - 1;
-            while (true) {
-                const unsigned long long w = wait_status64(&status[t], header);
-                excl += w >> 2;
-                if ((w & 3ull) == FLAG_INCL || t == 0) break;
-                --t;
-            }
-            st_volatile_u64(&status[tile], ((excl + total) << 2) | FLAG_INCL);
+        if (tile != 0) {
+            excl = warp_lookback<unsigned long long>(status, (int64_t)tile, header);
+            if (lane == 0) st_volatile_u64(&status[tile], ((excl + total) << 2) | FLAG_INCL);
         }
-        s_prefix = excl;
+        if (lane == 0) s_prefix = excl;
     }
     __syncthreads();
     const unsigned long long pre = s_prefix + warp_excl + (incl - mine);   // exclusive of this thread
@@ -229,6 +295,7 @@ constexpr size_t SORT_SMEM = (size_t)SORT_TILE * 4 + (size_t)SORT_TILE * 4 +
 // One stable 8-bit pass over (u32 key, u32 value) pairs: chained look-back over SORT_TILE-key
 // blocks ("onesweep"), in-block ranking by warp match. `n` is read from device memory; a count
 // above `capacity` (binning overflow) makes the pass a no-op.
+template <bool USE_MATCH>
 __global__ void __launch_bounds__(SORT_THREADS)
 sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
@@ -273,7 +340,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
     {
         uint32_t peers[SORT_ITEMS];   // independent MATCHes issued back to back (long latency)
 #pragma unroll
-        for (int k = 0; k < SORT_ITEMS; ++k) peers[k] = digit_peers(dr[k]);
+        for (int k = 0; k < SORT_ITEMS; ++k) peers[k] = USE_MATCH ? __match_any_sync(FULL_MASK, dr[k]) : digit_peers_ballot(dr[k]);
 #pragma unroll
         for (int k = 0; k < SORT_ITEMS; ++k) {
             // every lane reads its digit's running count (same-address reads broadcast), then the
@@ -329,13 +396,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
             st_volatile_u32(lb, (count << 2) | FLAG_INCL);
         } else {
             st_volatile_u32(lb, (count << 2) | FLAG_AGG);
-            int64_t t = (int64_t)tile - 1;
-            while (true) {
-                const uint32_t w = wait_status(lookback + (size_t)t * SORT_RADIX + tid, header);
-                excl += w >> 2;
-                if ((w & 3u) == FLAG_INCL || t == 0) break;
-                --t;
-            }
+            excl = thread_lookback(lookback + tid, SORT_RADIX, (int64_t)tile, header);
             st_volatile_u32(lb, ((excl + count) << 2) | FLAG_INCL);
         }
     }
@@ -422,22 +483,14 @@ sorted_scan_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __re
         if (w < warp) wex += t;
         total += t;
     }
-    if (tid == 0) {
+    if (warp == 0) {
+        if (lane == 0) st_volatile_u32(&status[block], (total << 2) | (block == 0 ? FLAG_INCL : FLAG_AGG));
         uint32_t excl = 0;
-        if (block == 0) {
-            st_volatile_u32(&status[0], (total << 2) | FLAG_INCL);
-        } else {
-            st_volatile_u32(&status[block], (total << 2) | FLAG_AGG);
-            int64_t t = (int64_t)block - 1;
-            while (true) {
-                const uint32_t w = wait_status(&status[t], header);
-                excl += w >> 2;
-                if ((w & 3u) == FLAG_INCL || t == 0) break;
-                --t;
-            }
-            st_volatile_u32(&status[block], ((excl + total) << 2) | FLAG_INCL);
+        if (block != 0) {
+            excl = warp_lookback<uint32_t>(status, (int64_t)block, header);
+            if (lane == 0) st_volatile_u32(&status[block], ((excl + total) << 2) | FLAG_INCL);
         }
-        s_prefix = excl;
+        if (lane == 0) s_prefix = excl;
     }
     __syncthreads();
     uint32_t run = s_prefix + wex + incl - tsum;     // global start of this thread's first run
@@ -574,10 +627,18 @@ tile_ranges_kernel(const uint32_t* __restrict__ keys, const B200sHeader* header,
 }
 
 // ------------------------------------------------------------------------ host launchers
+// Ranking primitive per pass: match.any costs grow with the number of DISTINCT digits in a warp, the
+// ballot form is flat. B200S_RANK_MATCH = bit mask over (which * 4 + pass), which: 0 depth, 1 tile.
+static bool rank_by_match(int which, int pass) {
+    static int mask = [] { const char* v = getenv("B200S_RANK_MATCH"); return v && *v ? (int)strtol(v, nullptr, 0) : 0xff; }();
+    return (mask >> (which * 4 + pass)) & 1;
+}
 static int set_sort_attr() {
     static bool attr_set = false;
     if (!attr_set) {
-        B200S_CUDA_OK(cudaFuncSetAttribute(sort_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        B200S_CUDA_OK(cudaFuncSetAttribute(sort_onesweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)SORT_SMEM));
+        B200S_CUDA_OK(cudaFuncSetAttribute(sort_onesweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)SORT_SMEM));
         attr_set = true;
     }
@@ -611,7 +672,8 @@ int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t 
         int cur = 0;
         for (int p = 0; p < DEPTH_PASSES; ++p) {
             count_launch();
-            sort_onesweep_kernel<<<(unsigned)g.depth_tiles, SORT_THREADS, SORT_SMEM, stream>>>(
+            auto kern = rank_by_match(0, p) ? sort_onesweep_kernel<true> : sort_onesweep_kernel<false>;
+            kern<<<(unsigned)g.depth_tiles, SORT_THREADS, SORT_SMEM, stream>>>(
                 g.vis_keys[cur], g.vis_ids[cur], g.vis_keys[cur ^ 1], g.vis_ids[cur ^ 1], g.header, n_ptr,
                 (int64_t)P, p * SORT_RADIX_BITS, g.depth_hist + p * SORT_RADIX,
                 g.depth_lookback + (size_t)p * g.depth_tiles * SORT_RADIX, g.counters + CTR_DEPTH_TICKET0 + p);
@@ -677,7 +739,8 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
         B200S_AFTER_LAUNCH(stream, debug);
         for (int p = 0; p < passes; ++p) {
             count_launch();
-            sort_onesweep_kernel<<<(unsigned)sort_tiles, SORT_THREADS, SORT_SMEM, stream>>>(
+            auto kern = rank_by_match(1, p) ? sort_onesweep_kernel<true> : sort_onesweep_kernel<false>;
+            kern<<<(unsigned)sort_tiles, SORT_THREADS, SORT_SMEM, stream>>>(
                 bw.keys[cur], bw.vals[cur], bw.keys[cur ^ 1], bw.vals[cur ^ 1], g.header, &g.header->num_rendered,
                 capacity, p * SORT_RADIX_BITS, bw.hist + p * SORT_RADIX,
                 bw.lookback + (size_t)p * bw.sort_tiles * SORT_RADIX, g.counters + CTR_SORT_TICKET0 + p);

@@ -375,6 +375,18 @@ __device__ __forceinline__ uint32_t digit_peers(uint32_t d) {
 #endif
 }
 
+// Ballot form for the 8-bit digits + sentinel bit (cost independent of the digit distribution).
+__device__ __forceinline__ uint32_t digit_peers_ballot(uint32_t d) {
+    uint32_t peers = FULL_MASK;
+#pragma unroll
+    for (int b = 0; b < 9; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t m = __ballot_sync(FULL_MASK, bit);
+        peers &= bit ? m : ~m;
+    }
+    return peers;
+}
+
 __device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
     uint32_t v;
     asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");

@@ -9,6 +9,7 @@
 // uninitialised allocations. SH rows are staged through shared memory with coalesced 16-B
 // transfers in both directions (read via cp.async, dL/dsh written back as full 128-B lines).
 
+#include <cstdlib>
 #include "kernels.cuh"
 
 namespace b200s {
@@ -87,8 +88,8 @@ __device__ __forceinline__ float3 sh_backward(int deg, float x, float y, float z
     return f3(dot(dx, dRGB), dot(dy, dRGB), dot(dz, dRGB));
 }
 
-template <bool SH16>
-__global__ void __launch_bounds__(PB_THREADS)
+template <bool SH16, int MINB>
+__global__ void __launch_bounds__(PB_THREADS, MINB)
 preprocess_bwd_kernel(const __grid_constant__ PreprocessBwdParams p) {
     extern __shared__ __align__(16) float sh_tile[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -360,17 +361,19 @@ int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream) {
                       (reinterpret_cast<uintptr_t>(p.shs) % 16 == 0) &&
                       (reinterpret_cast<uintptr_t>(p.dL_dsh) % 16 == 0);
     if (sh16) {
+        static int minb = [] { const char* v = getenv("B200S_PB_MINB"); return v && *v ? atoi(v) : 3; }();
+        auto kern = minb >= 4 ? preprocess_bwd_kernel<true, 4> : minb == 3 ? preprocess_bwd_kernel<true, 3>
+                                                                            : preprocess_bwd_kernel<true, 2>;
         static bool attr_set = false;
         if (!attr_set) {
-            B200S_CUDA_OK(cudaFuncSetAttribute(preprocess_bwd_kernel<true>,
-                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PB_SMEM_SH16));
+            B200S_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PB_SMEM_SH16));
             attr_set = true;
         }
         count_launch();
-        preprocess_bwd_kernel<true><<<blocks, PB_THREADS, PB_SMEM_SH16, stream>>>(p);
+        kern<<<blocks, PB_THREADS, PB_SMEM_SH16, stream>>>(p);
     } else {
         count_launch();
-        preprocess_bwd_kernel<false><<<blocks, PB_THREADS, 0, stream>>>(p);
+        preprocess_bwd_kernel<false, 2><<<blocks, PB_THREADS, 0, stream>>>(p);
     }
     return (int)cudaGetLastError();
 }

@@ -43,12 +43,19 @@ class GradientAllReduce:
 
     start(grads) enqueues every bucket asynchronously (after the producing stream's work, via an event);
     wait() makes the current stream wait for all of them. With the gloo backend (CPU tests) the same calls run
-    synchronously."""
+    synchronously.
+
+    Two ways to use it in a view loop:
+      blocking    start(g_k); wait()                      — the reduce is exposed after every step;
+      overlapped  wait(); start(g_k)  (+ a final wait())  — the reduce of view k runs on the NCCL stream while
+                  view k+1 is rasterized (the gradients of a backward are fresh tensors, so view k+1 does not
+                  touch the buffers in flight); the reduced gradients of view k are consumed one view late."""
 
     def __init__(self, group: Optional[dist.ProcessGroup] = None, max_bucket_bytes: int = 160 << 20):
         self.group = group
         self.max_bucket_bytes = int(max_bucket_bytes)
         self._works: list = []
+        self._held: list = []          # buckets being reduced: kept alive until wait()
         self._stream: Optional[torch.cuda.Stream] = None
         self._done: Optional[torch.cuda.Event] = None
 
@@ -75,6 +82,7 @@ class GradientAllReduce:
         if not dist.is_initialized() or dist.get_world_size(self.group) == 1:
             return
         bks = self.buckets(grads)
+        self._held = bks
         if bks and bks[0].is_cuda:
             dev = bks[0].device
             if self._stream is None:
@@ -98,6 +106,10 @@ class GradientAllReduce:
         if self._done is not None:
             torch.cuda.current_stream().wait_event(self._done)
             self._done = None
+        self._held = []
+
+    def pending(self) -> bool:
+        return self._done is not None or bool(self._works)
 
 
 def accumulate_(total: Dict[str, torch.Tensor], part: Dict[str, torch.Tensor]) -> None:

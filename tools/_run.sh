@@ -1,4 +1,1 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -5
-python tools/stage_times.py --cfg C3 --steps 10
-python tools/stage_times.py --cfg C2 --steps 10
-python tools/stage_times.py --cfg C4 --steps 10 --fwd-only
+for m in 2 3 4; do echo "PB_MINB=$m"; B200S_PB_MINB=$m python tools/stage_times.py --cfg C3 --steps 10; done
