@@ -123,7 +123,9 @@ _lib = None
 
 
 def lib_path() -> Path:
-    return _build.LIB_PATH
+    # B200S_LIB selects another in-tree build of the same sources (tuning variants, python build.py --tag NAME -D...)
+    alt = os.environ.get("B200S_LIB")
+    return Path(alt).resolve() if alt else _build.LIB_PATH
 
 
 def load() -> C.CDLL:

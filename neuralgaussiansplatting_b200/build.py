@@ -44,17 +44,25 @@ def _stale(target: Path, deps) -> bool:
     return any(Path(d).stat().st_mtime > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every kernel translation unit for sm_100a and link the shared library."""
+def build(force: bool = False, verbose: bool = False, extra_flags=(), tag: str = "") -> Path:
+    """Compile every kernel translation unit for sm_100a and link the shared library. `tag` builds a tuning
+    variant (extra -D flags) into _variants/libb200splat_<tag>.so without touching the product library."""
     nvcc = find_nvcc()
-    OBJ_DIR.mkdir(exist_ok=True)
+    global OBJ_DIR, LIB_PATH
+    obj_dir, lib_path = OBJ_DIR, LIB_PATH
+    if tag:
+        obj_dir = PKG_DIR / "_obj" / f"variant_{tag}"
+        (PKG_DIR / "_variants").mkdir(exist_ok=True)
+        lib_path = PKG_DIR / "_variants" / f"libb200splat_{tag}.so"
+        force = True
+    obj_dir.mkdir(parents=True, exist_ok=True)
     logs = {}
 
     def compile_one(src: str):
         s = CSRC / src
-        o = OBJ_DIR / (Path(src).stem + ".o")
+        o = obj_dir / (Path(src).stem + ".o")
         if force or _stale(o, [s, *HEADERS]):
-            cmd = [nvcc, *NVCC_FLAGS, "-I", str(INCLUDE), "-c", str(s), "-o", str(o)]
+            cmd = [nvcc, *NVCC_FLAGS, *extra_flags, "-I", str(INCLUDE), "-c", str(s), "-o", str(o)]
             r = subprocess.run(cmd, capture_output=True, text=True)
             logs[src] = r.stderr
             if r.returncode != 0:
@@ -63,8 +71,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    if force or _stale(LIB_PATH, objs):
-        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(LIB_PATH), *map(str, objs)]
+    if force or _stale(lib_path, objs):
+        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(lib_path), *map(str, objs)]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
@@ -72,10 +80,13 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         for k, v in logs.items():
             print(f"==== {k}\n{v}", file=sys.stderr)
     if logs:
-        (OBJ_DIR / "ptxas.log").write_text("".join(f"==== {k}\n{v}\n" for k, v in logs.items()))
-    return LIB_PATH
+        (obj_dir / "ptxas.log").write_text("".join(f"==== {k}\n{v}\n" for k, v in logs.items()))
+    return lib_path
 
 
 if __name__ == "__main__":
-    p = build(force="--force" in sys.argv, verbose=True)
+    # python build.py [--force] [--tag NAME -DFOO=1 ...]
+    argv = sys.argv[1:]
+    tag = argv[argv.index("--tag") + 1] if "--tag" in argv else ""
+    p = build(force="--force" in argv, verbose=not tag, extra_flags=[a for a in argv if a.startswith("-D")], tag=tag)
     print(p)

@@ -83,8 +83,15 @@ int env_int(const char* name, int dflt) {
     if (!v || !*v) return dflt;
     return atoi(v);
 }
-int blend_fwd_warps() { static int v = env_int("B200S_BLEND_FWD_WARPS", 2); return v; }
-int blend_bwd_warps() { static int v = env_int("B200S_BLEND_BWD_WARPS", 4); return v; }
+// Default: 2 warps per tile (fewest instructions per pair: a lane sums 4 pixels before the warp
+// reduction) unless the image has too few tiles to fill the 148 SMs with that many warps.
+int auto_warps(int tiles) {
+    int nw = 2;
+    while (nw < 8 && (int64_t)tiles * nw < 148 * 48) nw *= 2;
+    return nw;
+}
+int blend_fwd_warps(int tiles) { static int v = env_int("B200S_BLEND_FWD_WARPS", 0); return v > 0 ? v : auto_warps(tiles); }
+int blend_bwd_warps(int tiles) { static int v = env_int("B200S_BLEND_BWD_WARPS", 0); return v > 0 ? v : auto_warps(tiles); }
 
 struct Dims { int gx, gy, tiles; float focal_x, focal_y; };
 Dims dims_of(int W, int H, float tan_fovx, float tan_fovy) {
@@ -220,16 +227,17 @@ int b200s_forward_render(const B200sForwardArgs* a, b200s_stream_t stream_) {
     B200S_CUDA_OK(cudaMemsetAsync(g.counters + CTR_SORT_TICKET0, 0, SORT_MAX_PASSES * sizeof(uint32_t), stream));
     B200S_CUDA_OK(cudaMemsetAsync(g.counters + CTR_EXPAND_TICKET, 0, sizeof(uint32_t), stream));
     B200S_CUDA_OK(cudaMemsetAsync(g.exp_status, 0, 4 * ((size_t)(a->P + EXP_TILE - 1) / EXP_TILE + 1), stream));
-    rc = launch_binning(a->P, g, bw, a->bin_capacity, a->bin_capacity, d.gx, d.tiles, im.ranges, &final_buf,
-                        a->debug != 0, stream);
+    rc = launch_binning(a->P, g, bw, a->bin_capacity, a->bin_capacity, d.gx, d.tiles, im.ranges,
+                        &final_buf, a->debug != 0, stream);
     if (rc) return rc;
     BlendFwdParams b;
     b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;
-    b.ranges = im.ranges; b.point_list = bw.vals[final_buf]; b.rec = g.rec; b.background = a->background;
+    b.ranges = im.ranges; b.point_list = bw.vals[final_buf]; b.rec = g.rec;
+    b.background = a->background;
     b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last; b.out_color = a->out_color;
     {
         ProfScope ps(B200S_STAGE_BLEND_FWD, stream);
-        rc = launch_blend_fwd(b, blend_fwd_warps(), stream);
+        rc = launch_blend_fwd(b, blend_fwd_warps(d.tiles), stream);
     }
     if (rc) return rc;
     B200S_AFTER_LAUNCH(stream, a->debug);
@@ -287,13 +295,14 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
     if (a->num_rendered > 0) {
         BlendBwdParams b;
         b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;
-        b.ranges = im.ranges; b.point_list = bw.vals[final_buf]; b.rec = g.rec; b.point_offsets = g.point_offsets;
+        b.ranges = im.ranges; b.point_list = bw.vals[final_buf]; b.rec = g.rec;
+        b.point_offsets = g.point_offsets;
         b.background = a->background; b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last;
         b.dL_dpix = a->dL_dout_color; b.accum = ws.accum; b.partial = ws.partial; b.deterministic = a->deterministic;
         int rc;
         {
             ProfScope ps(B200S_STAGE_BLEND_BWD, stream);
-            rc = launch_blend_bwd(b, blend_bwd_warps(), stream);
+            rc = launch_blend_bwd(b, blend_bwd_warps(d.tiles), stream);
         }
         if (rc) return rc;
         B200S_AFTER_LAUNCH(stream, a->debug);

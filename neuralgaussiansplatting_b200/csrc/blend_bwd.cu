@@ -65,7 +65,7 @@ __device__ __forceinline__ float reduce9(float (&acc)[9], int lane, int& which) 
 }
 
 template <int NW, int SPT>
-__global__ void __launch_bounds__(32 * NW)
+__global__ void __launch_bounds__(32 * NW, bwd_min_blocks(NW))
 blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
     using WB = WarpBlocks<NW>;
     constexpr int PX = WB::PX, NX = WB::NX, NY = WB::NY;

@@ -20,6 +20,39 @@ constexpr float BLEND_ALPHA_MIN = 1.0f / 255.0f;
 #endif
 constexpr int BLEND_SPT = B200S_BLEND_SPT;   // list entries staged per thread per round
 
+// Minimum resident CTAs per SM requested from ptxas (register cap) per warps-per-tile variant
+// (B200S_{FWD,BWD}_MINB{1,2,4,8}; 1 = no cap).
+#ifndef B200S_FWD_MINB1
+#define B200S_FWD_MINB1 16
+#endif
+#ifndef B200S_FWD_MINB2
+#define B200S_FWD_MINB2 16
+#endif
+#ifndef B200S_FWD_MINB4
+#define B200S_FWD_MINB4 8
+#endif
+#ifndef B200S_FWD_MINB8
+#define B200S_FWD_MINB8 1
+#endif
+#ifndef B200S_BWD_MINB1
+#define B200S_BWD_MINB1 16
+#endif
+#ifndef B200S_BWD_MINB2
+#define B200S_BWD_MINB2 12
+#endif
+#ifndef B200S_BWD_MINB4
+#define B200S_BWD_MINB4 8
+#endif
+#ifndef B200S_BWD_MINB8
+#define B200S_BWD_MINB8 1
+#endif
+constexpr int fwd_min_blocks(int nw) {
+    return nw == 1 ? B200S_FWD_MINB1 : nw == 2 ? B200S_FWD_MINB2 : nw == 4 ? B200S_FWD_MINB4 : B200S_FWD_MINB8;
+}
+constexpr int bwd_min_blocks(int nw) {
+    return nw == 1 ? B200S_BWD_MINB1 : nw == 2 ? B200S_BWD_MINB2 : nw == 4 ? B200S_BWD_MINB4 : B200S_BWD_MINB8;
+}
+
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem_src) : "memory");

@@ -24,7 +24,7 @@ namespace b200s {
 constexpr float ALPHA_MIN = BLEND_ALPHA_MIN;
 
 template <int NW, int SPT>
-__global__ void __launch_bounds__(32 * NW)
+__global__ void __launch_bounds__(32 * NW, fwd_min_blocks(NW))
 blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     using WB = WarpBlocks<NW>;
     constexpr int PX = WB::PX, NX = WB::NX, NY = WB::NY;
