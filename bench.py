@@ -201,7 +201,18 @@ def run_ours(args, rank, local_rank, world, dev):
     lib = _lib.load()          # raises if libb200splat.so is missing: there is no fallback path
     w = Workload(args.workload, dev, rank, world)
     cfg = w.cfg
-    reducer = parallel.GradientAllReduce() if world > 1 else None
+    reducer, collective_kind = None, "none"
+    if world > 1:
+        if args.collective == "peer":
+            # the collective is one kernel of libb200splat.so over NVLink peer memory; the backward writes its
+            # gradients straight into the peer-mapped buffers (no staging copy, no NCCL call in the step)
+            reducer = parallel.PeerGradientAllReduce(w.P, 16, dev, ctas=args.peer_ctas, multimem=args.multimem)
+            _C.config["grad_out"] = reducer.grad_out
+            collective_kind = (f"b200s_peer_allreduce_sum_f32 ({'multimem/NVLS' if reducer.multimem else 'P2P two-shot'}, "
+                               f"{reducer.ctas} CTAs, {reducer.mem.backend} mappings)")
+        else:
+            reducer = parallel.GradientAllReduce()
+            collective_kind = "NCCL all_reduce (per-tensor buckets)"
     GRAD_KEYS = {"means3D": 3, "opacities": 2, "shs": 5, "scales": 6, "rotations": 7}   # slots of the 8-tuple
 
     overlap = args.allreduce == "overlap"
@@ -299,12 +310,13 @@ def run_ours(args, rank, local_rank, world, dev):
         "ms_per_step": round(ms_total / args.steps, 4), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{cfg.name}: {w.P} Gaussians SH3, {cfg.width}x{cfg.height}, fwd+bwd, 1 view/step/GPU "
-                               f"cycling {w.nviews} orbit views" + (", + NCCL SUM all-reduce of 59 floats/Gaussian"
+                               f"cycling {w.nviews} orbit views" + (", + SUM all-reduce of 59 floats/Gaussian"
                                                                      if world > 1 else ""),
                    "allreduce": ("none (1 GPU)" if world == 1 else
-                                 "overlap: the reduce of view k runs on the NCCL stream while view k+1 is rasterized "
+                                 "overlap: the reduce of view k runs on a side stream while view k+1 is rasterized "
                                  "(north_star); every reduce completes inside the timed region" if overlap else
                                  "blocking: reduce exposed after every view"),
+                   "collective": collective_kind,
                    "parallelism": f"view-parallel x{world}, Gaussians replicated",
                    "l2": "inputs (708 MB of Gaussian parameters) exceed the 126 MB L2; no explicit flush",
                    "blend_mode": "strict (expf, bit-exact n_contrib)"},
@@ -528,6 +540,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
+                    help="N>1, our arm: gradient all-reduce as the library's own NVLink peer-memory kernel, or NCCL")
+    ap.add_argument("--peer-ctas", type=int, default=32)
+    ap.add_argument("--multimem", action="store_true", help="peer collective: NVSwitch multimem.ld_reduce/st")
     ap.add_argument("--allreduce", default="overlap", choices=["overlap", "blocking"],
                     help="N>1: overlap the gradient all-reduce of view k with the rasterization of view k+1")
     args = ap.parse_args()

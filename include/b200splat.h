@@ -246,8 +246,37 @@ uint64_t b200s_launch_count(void);
  * (sum of n_contrib). counts_dev: device u64[3]. */
 int b200s_count_pairs(const B200sForwardArgs* args, unsigned long long* counts_dev, b200s_stream_t stream);
 
+/* ---- gradient all-reduce over NVLink peer memory (the one collective of the
+ *      path; the reference has no multi-GPU code, utils/general_utils.py:133 — the baseline
+ *      this replaces is ncclAllReduce(sum, fp32) over the 59 gradient floats per Gaussian).
+ *      One launch: cross-rank start barrier, two-shot fixed-order sum (rank r reduces slice r
+ *      from every peer and stores the total to every peer), end barrier. Every rank of the
+ *      group must call it with the same n_floats / ctas / epoch, in the same order.
+ *      peer_bufs[r]  : rank r's gradient buffer as mapped into THIS process (symmetric
+ *                      allocation; peer_bufs[rank] is the local one), 16-byte aligned.
+ *      peer_flags[r] : rank r's flag array (u32, >= b200s_peer_allreduce_flag_bytes, zeroed
+ *                      once at allocation), same mapping rules.
+ *      multicast_buf : NVSwitch multicast mapping of the buffer or NULL; used only when
+ *                      use_multimem != 0 (multimem.ld_reduce / multimem.st; the switch sums).
+ *      epoch         : strictly increasing per call (1, 2, ...) — flags are never reset.
+ *      In-place: after the call (stream-ordered) every rank's buffer holds the sum. */
+#define B200S_MAX_PEERS 16
+typedef struct B200sPeerReduceArgs {
+    void* peer_bufs[B200S_MAX_PEERS];
+    void* peer_flags[B200S_MAX_PEERS];
+    void* multicast_buf;
+    uint64_t n_floats;       /* multiple of 4 */
+    int32_t rank, world;
+    uint32_t epoch;
+    int32_t ctas;            /* CTAs of 512 threads the collective may occupy (1..1024) */
+    int32_t use_multimem;
+    int32_t reserved;
+} B200sPeerReduceArgs;
+size_t b200s_peer_allreduce_flag_bytes(int32_t ctas, int32_t world);
+int b200s_peer_allreduce_sum_f32(const B200sPeerReduceArgs* args, b200s_stream_t stream);
+
 /* sizeof() of the ABI structs as compiled: 0 B200sHeader, 1 B200sForwardArgs,
- * 2 B200sBackwardArgs, 3 B200sIdxmapArgs. Bindings assert their own layout against it. */
+ * 2 B200sBackwardArgs, 3 B200sIdxmapArgs, 4 B200sPeerReduceArgs. Bindings assert their own layout against it. */
 size_t b200s_sizeof(int32_t which);
 
 /* Library / build identification. */

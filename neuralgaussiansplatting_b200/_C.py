@@ -26,7 +26,10 @@ NUM_FEATURES = 64
 #   optimistic   : size the binning workspace from the previous call of the same shape and
 #                  enqueue the whole forward without the reference's mid-pipeline host sync
 #                  (rasterizer_impl.cu:281); falls back to an exact re-run on overflow.
-config = {"deterministic": False, "optimistic": True, "growth": 1.25}
+# grad_out: None, or a callable returning {"means3D","opacities","shs","scales","rotations"} -> preallocated float32
+# CUDA tensors the backward writes its gradients into (parallel.PeerGradientAllReduce.grad_out: peer-mapped
+# buffers, so the all-reduce kernel sums them in place with no staging copy).
+config = {"deterministic": False, "optimistic": True, "growth": 1.25, "grad_out": None}
 
 _tls = threading.local()
 _capacity_hint = {}   # (device index, P, W, H) -> last num_rendered
@@ -173,12 +176,22 @@ def _backward_impl(background, means3D, radii, colors, scales, rotations, scale_
     with torch.cuda.device(dev):
         has_sh = sh.numel() != 0
         has_sr = scales.numel() != 0
-        g_means3D = torch.empty((P, 3), **f32)
+        pre = config["grad_out"]() if (config["grad_out"] is not None and has_sh and has_sr) else {}
+
+        def out(name, shape):
+            t = pre.get(name)
+            if t is None:
+                return torch.empty(shape, **f32)
+            if tuple(t.shape) != tuple(shape) or t.dtype != torch.float32 or t.device != dev or not t.is_contiguous():
+                raise RuntimeError(f"config['grad_out'][{name!r}] must be a contiguous float32 {tuple(shape)} tensor on {dev}")
+            return t
+
+        g_means3D = out("means3D", (P, 3))
         g_means2D = torch.empty((P, 3), **f32)
-        g_opacity = torch.empty((P, 1), **f32)
-        g_sh = torch.empty((P, M, 3), **f32) if has_sh else torch.zeros((P, M, 3), **f32)
-        g_scales = torch.empty((P, 3), **f32) if has_sr else torch.zeros((P, 3), **f32)
-        g_rot = torch.empty((P, 4), **f32) if has_sr else torch.zeros((P, 4), **f32)
+        g_opacity = out("opacities", (P, 1))
+        g_sh = out("shs", (P, M, 3)) if has_sh else torch.zeros((P, M, 3), **f32)
+        g_scales = out("scales", (P, 3)) if has_sr else torch.zeros((P, 3), **f32)
+        g_rot = out("rotations", (P, 4)) if has_sr else torch.zeros((P, 4), **f32)
         g_colors = torch.empty((P, NUM_CHANNELS), **f32) if (want_all or not has_sh) else None
         g_cov3D = torch.empty((P, 6), **f32) if (want_all or not has_sr) else None
         if P == 0:

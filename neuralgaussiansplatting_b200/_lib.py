@@ -77,6 +77,18 @@ class IdxmapArgs(C.Structure):
     ]
 
 
+MAX_PEERS = 16
+
+
+class PeerReduceArgs(C.Structure):
+    _fields_ = [
+        ("peer_bufs", C.c_void_p * MAX_PEERS), ("peer_flags", C.c_void_p * MAX_PEERS),
+        ("multicast_buf", C.c_void_p), ("n_floats", C.c_uint64),
+        ("rank", C.c_int32), ("world", C.c_int32), ("epoch", C.c_uint32), ("ctas", C.c_int32),
+        ("use_multimem", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
 STATE = {
     "depths": 0, "means2D": 1, "conic_opacity": 2, "rgb": 3, "tiles_touched": 4, "point_offsets": 5,
     "point_list": 6, "point_list_keys": 7, "ranges": 8, "n_contrib": 9, "final_T": 10, "clamped": 11,
@@ -116,6 +128,8 @@ SYMBOLS = [
     ("b200s_profile_end", C.c_int, [C.c_void_p, C.c_void_p]),
     ("b200s_launch_count", C.c_uint64, []),
     ("b200s_count_pairs", C.c_int, [C.POINTER(ForwardArgs), C.c_void_p, C.c_void_p]),
+    ("b200s_peer_allreduce_flag_bytes", C.c_size_t, [C.c_int32, C.c_int32]),
+    ("b200s_peer_allreduce_sum_f32", C.c_int, [C.POINTER(PeerReduceArgs), C.c_void_p]),
     ("b200s_export_state", C.c_int64, [C.POINTER(ForwardArgs), C.c_int32, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
 ]
 
@@ -145,7 +159,7 @@ def load() -> C.CDLL:
         fn.argtypes = argtypes
     if lib.b200s_abi_version() != 1:
         raise RuntimeError("libb200splat.so ABI version mismatch")
-    for which, struct in enumerate((Header, ForwardArgs, BackwardArgs, IdxmapArgs)):
+    for which, struct in enumerate((Header, ForwardArgs, BackwardArgs, IdxmapArgs, PeerReduceArgs)):
         if lib.b200s_sizeof(which) != C.sizeof(struct):
             raise RuntimeError(f"ctypes layout of {struct.__name__} does not match the library")
     _lib = lib

@@ -167,6 +167,7 @@ size_t b200s_sizeof(int32_t which) {
         case 1: return sizeof(B200sForwardArgs);
         case 2: return sizeof(B200sBackwardArgs);
         case 3: return sizeof(B200sIdxmapArgs);
+        case 4: return sizeof(B200sPeerReduceArgs);
         default: return 0;
     }
 }
@@ -353,6 +354,21 @@ int b200s_idxmap_backward(int32_t P, int32_t W, int32_t H, const int32_t* out_id
 }
 
 }  // extern "C"
+
+extern "C" size_t b200s_peer_allreduce_flag_bytes(int32_t ctas, int32_t world) {
+    if (ctas <= 0 || world <= 0) return 0;
+    return (size_t)2 * (size_t)ctas * (size_t)world * sizeof(uint32_t);   // two barrier phases
+}
+
+extern "C" int b200s_peer_allreduce_sum_f32(const B200sPeerReduceArgs* a, b200s_stream_t stream_) {
+    if (!a || a->world < 1 || a->world > B200S_MAX_PEERS || a->rank < 0 || a->rank >= a->world) return B200S_E_BADARG;
+    if (a->ctas < 1 || a->ctas > 1024 || (a->n_floats & 3u) || a->epoch == 0) return B200S_E_BADARG;
+    if (a->use_multimem && !a->multicast_buf) return B200S_E_BADARG;
+    for (int r = 0; r < a->world; ++r)
+        if (!a->peer_bufs[r] || !a->peer_flags[r] || ((uintptr_t)a->peer_bufs[r] & 15u)) return B200S_E_BADARG;
+    if (a->n_floats == 0 || a->world == 1) return 0;
+    return launch_peer_allreduce(*a, (cudaStream_t)stream_);
+}
 
 extern "C" int b200s_count_pairs(const B200sForwardArgs* a, unsigned long long* counts_dev, b200s_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;

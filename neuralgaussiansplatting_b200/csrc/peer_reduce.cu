@@ -1,0 +1,185 @@
+// Gradient all-reduce over NVLink peer memory (the one collective of the path —
+// a SUM of the 59 gradient floats per Gaussian across the view-parallel ranks). The reference has
+// no multi-GPU code (utils/general_utils.py:133); the baseline this replaces is ncclAllReduce.
+//
+// Every rank holds the gradient buffer at the same offset of a symmetric allocation whose peer
+// mappings (and, on NVSwitch, one multicast mapping) are passed in. preprocess_bwd writes its
+// outputs straight into that buffer; this kernel then runs the whole collective in ONE launch:
+//
+//   start barrier   CTA b of every rank tells CTA b of every peer "my gradients are complete"
+//   two-shot sum    rank r owns elements [r*n/world, (r+1)*n/world): it reads that slice from every
+//                   rank in rank order (fixed-order fp32 sum -> every replica gets bit-identical
+//                   values, run to run), and stores the total into every rank's buffer
+//                   (multimem mode: one multimem.ld_reduce + one multimem.st per 16 bytes instead;
+//                   the NVSwitch adds and replicates)
+//   end barrier     CTA b waits until CTA b of every peer has stored its slice here
+//
+// Per GPU and direction this moves (world-1)/world * n bytes over NVLink, the minimum for an
+// all-reduce without in-switch reduction, and it occupies only `ctas` CTAs of 512 threads, so the
+// next view's rasterization keeps (almost) all SMs while the gradients of this one are summed.
+// Flags are monotonically increasing epochs in a second symmetric allocation; no reset is needed.
+
+#include "kernels.cuh"
+
+namespace b200s {
+
+constexpr int PR_THREADS = 512;
+
+struct PeerReduceParams {
+    float4* bufs[B200S_MAX_PEERS];
+    uint32_t* flags[B200S_MAX_PEERS];
+    float4* mc;            // multicast mapping of the same buffer, or NULL
+    size_t n4;             // float4 elements
+    int rank, world;
+    uint32_t epoch;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// Data accesses are WEAK (plain LDG/STG; .STRONG.SYS accesses measured 2x slower over NVLink): every address is
+// read at most once per launch and only after the start barrier (acquire + bar.sync), and the stores are made
+// visible by the end barrier's fence.sys + release.
+__device__ __forceinline__ float4 ld_peer(const float4* p) {
+    float4 v;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_peer(float4* p, const float4& v) {
+    asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 multimem_ld_reduce(const float4* p) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.weak.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st(float4* p, const float4& v) {
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// Flag slot written by (phase, cta, source rank) in the DESTINATION rank's flag array.
+__device__ __forceinline__ size_t flag_slot(int phase, int cta, int ctas, int src, int world) {
+    return ((size_t)phase * ctas + cta) * world + src;
+}
+
+// All ranks' CTA `blockIdx.x` meet. Threads 0..world-1 each handle one peer.
+__device__ __forceinline__ void peer_barrier(const PeerReduceParams& p, int phase) {
+    __syncthreads();
+    if ((int)threadIdx.x < p.world) {
+        const int peer = threadIdx.x;
+        __threadfence_system();
+        st_release_sys(p.flags[peer] + flag_slot(phase, blockIdx.x, gridDim.x, p.rank, p.world), p.epoch);
+        const uint32_t* mine = p.flags[p.rank] + flag_slot(phase, blockIdx.x, gridDim.x, peer, p.world);
+        while ((int32_t)(ld_acquire_sys(mine) - p.epoch) < 0) __nanosleep(64);
+    }
+    __syncthreads();
+}
+
+template <int WORLD, bool MULTIMEM>
+__global__ void __launch_bounds__(PR_THREADS)
+peer_allreduce_kernel(const __grid_constant__ PeerReduceParams p) {
+    const int world = WORLD > 0 ? WORLD : p.world;
+    peer_barrier(p, 0);
+
+    const size_t per = (p.n4 + world - 1) / world;
+    const size_t begin = min(p.n4, per * (size_t)p.rank);
+    const size_t end = min(p.n4, begin + per);
+    const size_t stride = (size_t)gridDim.x * PR_THREADS;
+    constexpr int U = MULTIMEM ? 8 : (WORLD > 0 && WORLD <= 2 ? 8 : WORLD > 0 && WORLD <= 4 ? 4 : 2);
+
+    for (size_t i0 = begin + (size_t)blockIdx.x * PR_THREADS + threadIdx.x; i0 < end; i0 += stride * U) {
+        float4 acc[U];
+        if (MULTIMEM) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const size_t i = i0 + u * stride;
+                if (i < end) acc[u] = multimem_ld_reduce(p.mc + i);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const size_t i = i0 + u * stride;
+                if (i < end) multimem_st(p.mc + i, acc[u]);
+            }
+        } else {
+            float4 v[U][WORLD > 0 ? WORLD : 1];
+            if (WORLD > 0) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const size_t i = i0 + u * stride;
+#pragma unroll
+                    for (int r = 0; r < WORLD; ++r)
+                        if (i < end) v[u][r] = ld_peer(p.bufs[r] + i);
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    acc[u] = v[u][0];
+#pragma unroll
+                    for (int r = 1; r < WORLD; ++r) {
+                        acc[u].x += v[u][r].x; acc[u].y += v[u][r].y; acc[u].z += v[u][r].z; acc[u].w += v[u][r].w;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const size_t i = i0 + u * stride;
+                    if (i >= end) continue;
+                    acc[u] = ld_peer(p.bufs[0] + i);
+                    for (int r = 1; r < world; ++r) {
+                        const float4 t = ld_peer(p.bufs[r] + i);
+                        acc[u].x += t.x; acc[u].y += t.y; acc[u].z += t.z; acc[u].w += t.w;
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const size_t i = i0 + u * stride;
+                if (i < end) {
+                    if (WORLD > 0) {
+#pragma unroll
+                        for (int r = 0; r < WORLD; ++r) st_peer(p.bufs[r] + i, acc[u]);
+                    } else {
+                        for (int r = 0; r < world; ++r) st_peer(p.bufs[r] + i, acc[u]);
+                    }
+                }
+            }
+        }
+    }
+    peer_barrier(p, 1);
+}
+
+template <int WORLD, bool MM>
+static int launch_pr(const PeerReduceParams& p, int ctas, cudaStream_t stream) {
+    count_launch();
+    peer_allreduce_kernel<WORLD, MM><<<ctas, PR_THREADS, 0, stream>>>(p);
+    return (int)cudaGetLastError();
+}
+
+int launch_peer_allreduce(const B200sPeerReduceArgs& a, cudaStream_t stream) {
+    PeerReduceParams p{};
+    for (int r = 0; r < a.world; ++r) {
+        p.bufs[r] = (float4*)a.peer_bufs[r];
+        p.flags[r] = (uint32_t*)a.peer_flags[r];
+    }
+    p.mc = (float4*)a.multicast_buf;
+    p.n4 = (size_t)(a.n_floats / 4);
+    p.rank = a.rank; p.world = a.world; p.epoch = a.epoch;
+    const int ctas = a.ctas;
+    if (a.use_multimem) return launch_pr<0, true>(p, ctas, stream);
+    switch (a.world) {
+        case 2: return launch_pr<2, false>(p, ctas, stream);
+        case 4: return launch_pr<4, false>(p, ctas, stream);
+        case 8: return launch_pr<8, false>(p, ctas, stream);
+        default: return launch_pr<0, false>(p, ctas, stream);
+    }
+}
+
+}  // namespace b200s

@@ -112,6 +112,188 @@ class GradientAllReduce:
         return self._done is not None or bool(self._works)
 
 
+def gradient_layout(P: int, sh_coeffs: int = 16, align_floats: int = 64):
+    """Offsets (in floats) of the five gradient tensors inside one flat peer buffer, each sub-tensor starting on a
+    256-byte boundary (preprocess_bwd stores dL/dsh rows as 16-byte vectors). Returns ({name: (offset, shape)},
+    total_floats) with total_floats a multiple of `align_floats`."""
+    shapes = {"means3D": (P, 3), "opacities": (P, 1), "scales": (P, 3), "rotations": (P, 4), "shs": (P, sh_coeffs, 3)}
+    out, off = {}, 0
+    for name in PARAM_ORDER:
+        n = 1
+        for d in shapes[name]:
+            n *= d
+        out[name] = (off, shapes[name])
+        off = -(-(off + n) // align_floats) * align_floats
+    return out, off
+
+
+class PeerMemory:
+    """`nbytes` of device memory on every rank of the group, each rank's block mapped into every other rank's
+    address space over NVLink (plumbing only: the kernels that use the mappings are in libb200splat.so).
+
+    backend "symm": torch.distributed._symmetric_memory (cuMem + fabric/fd handle exchange; also yields the
+    NVSwitch multicast mapping when the box has one). backend "ipc": legacy CUDA IPC handles of a plain torch
+    allocation exchanged through the process group. "auto" tries symm first; all ranks agree on the outcome."""
+
+    def __init__(self, nbytes: int, device, group=None, backend: str = "auto"):
+        self.group = group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.nbytes = int(nbytes)
+        self.device = torch.device(device)
+        self.multicast_ptr = 0
+        self.backend = None
+        self._keep = []
+        err = None
+        if backend in ("auto", "symm"):
+            try:
+                self._init_symm()
+            except Exception as e:  # noqa: BLE001 - any failure means "not available on this box"
+                err = e
+            ok = torch.tensor([1 if self.backend == "symm" else 0], device=self.device, dtype=torch.int32)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok.item()) == 0:
+                self.backend = None
+                self.multicast_ptr = 0
+                if backend == "symm":
+                    raise RuntimeError(f"symmetric memory is not available on every rank: {err}")
+        if self.backend is None:
+            self._init_ipc()
+
+    def _init_symm(self):
+        import torch.distributed._symmetric_memory as symm_mem
+        grp = self.group if self.group is not None else dist.group.WORLD
+        t = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+        hdl = symm_mem.rendezvous(t, grp)
+        self.local = t
+        self.ptrs = [int(x) for x in hdl.buffer_ptrs]
+        if getattr(hdl, "has_multicast_support", False):
+            self.multicast_ptr = int(hdl.multicast_ptr or 0)
+        self._keep = [hdl]
+        self.backend = "symm"
+
+    def _init_ipc(self):
+        t = torch.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+        meta = t.untyped_storage()._share_cuda_()
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, (meta, t.storage_offset()), group=self.group)
+        self.local = t
+        self.ptrs = []
+        for r, (m, off) in enumerate(gathered):
+            if r == self.rank:
+                self.ptrs.append(t.data_ptr())
+                continue
+            m = list(m)
+            m[0] = self.device.index if self.device.index is not None else torch.cuda.current_device()
+            with torch.cuda.device(self.device):
+                st = torch.UntypedStorage._new_shared_cuda(*m)
+            self._keep.append(st)
+            self.ptrs.append(st.data_ptr() + off)
+        self.backend = "ipc"
+        dist.barrier(group=self.group)
+
+
+class PeerGradientAllReduce:
+    """The gradient all-reduce as ONE kernel of libb200splat.so over NVLink peer memory
+    (b200s_peer_allreduce_sum_f32, csrc/peer_reduce.cu) instead of NCCL calls.
+
+    The rasterizer's backward writes its five gradient tensors straight into a peer-mapped buffer
+    (`grad_out()` hands `_C.config["grad_out"]` fresh views; buffers rotate so the reduce of view k can run while
+    view k+1 is written). start(grads) launches the collective on a high-priority side stream after the producing
+    stream's work; wait() makes the current stream wait for it. Sums are taken in rank order by a single owner
+    per element, so every replica receives bit-identical values and results are reproducible run to run.
+    Same start()/wait() protocol as GradientAllReduce. Gradients that do not alias the current buffer (autograd
+    cloned them) are copied in and back out."""
+
+    def __init__(self, P: int, sh_coeffs: int = 16, device=None, group=None, n_buffers: int = 2, ctas: int = 32,
+                 multimem: bool = False, backend: str = "auto"):
+        from . import _lib
+        self._libmod = _lib
+        self._lib = _lib.load()
+        self.group = group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if self.world > _lib.MAX_PEERS:
+            raise ValueError(f"at most {_lib.MAX_PEERS} peers")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.layout, self.n_floats = gradient_layout(P, sh_coeffs)
+        self.n_buffers, self.ctas = int(n_buffers), int(ctas)
+        self.flag_bytes = -(-int(self._lib.b200s_peer_allreduce_flag_bytes(self.ctas, self.world)) // 256) * 256
+        self.buf_bytes = self.n_floats * 4
+        self.mem = PeerMemory(self.flag_bytes + self.n_buffers * self.buf_bytes, self.device, group, backend)
+        self.mem.local.zero_()
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=group)                      # nobody raises a flag before every flag array is zero
+        self.multimem = bool(multimem) and self.mem.multicast_ptr != 0
+        self._flat = [self.mem.local[self.flag_bytes + i * self.buf_bytes: self.flag_bytes + (i + 1) * self.buf_bytes]
+                      .view(torch.float32) for i in range(self.n_buffers)]
+        self._cur = -1
+        self._epoch = 0
+        self._stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self._done: Optional[torch.cuda.Event] = None
+        self._copy_back = None
+
+    # ---- buffers
+    def _views(self, i: int) -> Dict[str, torch.Tensor]:
+        flat = self._flat[i]
+        out = {}
+        for name, (off, shape) in self.layout.items():
+            n = 1
+            for d in shape:
+                n *= d
+            out[name] = flat[off:off + n].view(shape)
+        return out
+
+    def grad_out(self) -> Dict[str, torch.Tensor]:
+        """Rotate to the next buffer and return fresh views of it (install as `_C.config["grad_out"]`)."""
+        self._cur = (self._cur + 1) % self.n_buffers
+        return self._views(self._cur)
+
+    # ---- collective
+    def start(self, grads: Optional[Dict[str, torch.Tensor]] = None) -> None:
+        if self._cur < 0:
+            self._cur = 0
+        views = self._views(self._cur)
+        self._copy_back = None
+        if grads is not None:
+            stray = {k: g for k, g in grads.items() if g is not None and k in views
+                     and g.data_ptr() != views[k].data_ptr()}
+            if stray:
+                for k, g in stray.items():
+                    views[k].copy_(g.reshape(views[k].shape))
+                self._copy_back = (stray, views)
+        a = self._libmod.PeerReduceArgs()
+        off = self.flag_bytes + self._cur * self.buf_bytes
+        for r in range(self.world):
+            a.peer_bufs[r] = self.mem.ptrs[r] + off
+            a.peer_flags[r] = self.mem.ptrs[r]
+        a.multicast_buf = (self.mem.multicast_ptr + off) if self.multimem else None
+        a.n_floats = self.n_floats
+        a.rank, a.world = self.rank, self.world
+        self._epoch += 1
+        a.epoch = self._epoch
+        a.ctas = self.ctas
+        a.use_multimem = int(self.multimem)
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream(self.device))
+        self._stream.wait_event(ready)
+        self._libmod.check(self._lib.b200s_peer_allreduce_sum_f32(a, self._stream.cuda_stream),
+                           "b200s_peer_allreduce_sum_f32")
+        self._done = torch.cuda.Event()
+        self._done.record(self._stream)
+
+    def wait(self) -> None:
+        if self._done is not None:
+            torch.cuda.current_stream(self.device).wait_event(self._done)
+            self._done = None
+        if self._copy_back is not None:
+            stray, views = self._copy_back
+            for k, g in stray.items():
+                g.copy_(views[k].reshape(g.shape))
+            self._copy_back = None
+
+    def pending(self) -> bool:
+        return self._done is not None
+
+
 def accumulate_(total: Dict[str, torch.Tensor], part: Dict[str, torch.Tensor]) -> None:
     for k, v in part.items():
         if v is None:
