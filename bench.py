@@ -209,7 +209,9 @@ def run_ours(args, rank, local_rank, world, dev):
             reducer = parallel.PeerGradientAllReduce(w.P, 16, dev, ctas=args.peer_ctas, multimem=args.multimem)
             _C.config["grad_out"] = reducer.grad_out
             collective_kind = (f"b200s_peer_allreduce_sum_f32 ({'multimem/NVLS' if reducer.multimem else 'P2P two-shot'}, "
-                               f"{reducer.ctas} CTAs, {reducer.mem.backend} mappings)")
+                               f"{reducer.ctas} CTAs, {reducer.mem.backend} mappings"
+                               + ("" if args.dense_collective or reducer.multimem else
+                                  ", dL/dSH rows read only from ranks whose view saw the Gaussian (radii > 0)") + ")")
         else:
             reducer = parallel.GradientAllReduce()
             collective_kind = "NCCL all_reduce (per-tensor buckets)"
@@ -217,14 +219,17 @@ def run_ours(args, rank, local_rank, world, dev):
 
     overlap = args.allreduce == "overlap"
 
-    def reduce_step(grads):
+    sparse = world > 1 and args.collective == "peer" and not args.dense_collective
+
+    def reduce_step(grads, radii=None):
         if reducer is None:
             return
+        kw = {"radii": radii} if (sparse and radii is not None) else {}
         if overlap:
             reducer.wait()          # the reduce of the PREVIOUS view ran while this view was rasterized
-            reducer.start(grads)
+            reducer.start(grads, **kw)
         else:
-            reducer.start(grads)
+            reducer.start(grads, **kw)
             reducer.wait()
 
     def reduce_finalize():
@@ -239,7 +244,7 @@ def run_ours(args, rank, local_rank, world, dev):
                                             fa[10], fa[11], w.dL[v], fa[14], fa[15], fa[16], out[3], out[0], out[4],
                                             out[5], False)
         if collective:
-            reduce_step({k: g[i] for k, i in GRAD_KEYS.items()})
+            reduce_step({k: g[i] for k, i in GRAD_KEYS.items()}, radii=out[2])
         return g
 
     # ---- e2e: the call a user makes (nn.Module + autograd). Every step's host inputs (camera block + ground-truth
@@ -276,7 +281,7 @@ def run_ours(args, rank, local_rank, world, dev):
                                                   cov3D_precomp=None)
         loss = (img - gt_dev).abs().mean()
         loss.backward()
-        reduce_step({k: p.grad for k, p in params.items()})
+        reduce_step({k: p.grad for k, p in params.items()}, radii=radii)
         if losses.push(loss) is not None:                 # loss of the previous step is now on the host
             state["read"] += 1
         for p in params.values():
@@ -542,7 +547,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1, our arm: gradient all-reduce as the library's own NVLink peer-memory kernel, or NCCL")
-    ap.add_argument("--peer-ctas", type=int, default=32)
+    ap.add_argument("--peer-ctas", type=int, default=16)
+    ap.add_argument("--dense-collective", action="store_true",
+                    help="peer collective: do not use the view's radii to skip all-zero dL/dSH rows")
     ap.add_argument("--multimem", action="store_true", help="peer collective: NVSwitch multimem.ld_reduce/st")
     ap.add_argument("--allreduce", default="overlap", choices=["overlap", "blocking"],
                     help="N>1: overlap the gradient all-reduce of view k with the rasterization of view k+1")

@@ -270,9 +270,24 @@ typedef struct B200sPeerReduceArgs {
     uint32_t epoch;
     int32_t ctas;            /* CTAs of 512 threads the collective may occupy (1..1024) */
     int32_t use_multimem;
-    int32_t reserved;
+    /* Visibility-sparse tail (optional; radii == NULL reduces everything densely). The LAST tensor of the
+     * buffer, floats [sparse_offset_floats, sparse_offset_floats + 48*sparse_rows) with at most alignment padding
+     * (left untouched) up to n_floats, is sparse_rows rows of 48 floats (dL/dSH, degree 3).
+     * radii: THIS rank's radii[sparse_rows] (int32, the forward's output for the view the gradients belong
+     * to): rows with radii <= 0 are all-zero on this rank (b200s_backward zero-fills them) and are neither read
+     * by the owners nor, if no rank saw them, written. vis_offset_bytes: offset from peer_bufs[r] of a
+     * b200s_peer_allreduce_vis_bytes() scratch array inside the same peer mapping (zeroed once at allocation).
+     * Used for world in {2, 4, 8} without multimem; the result is bit-identical to the dense reduction. */
+    int32_t sparse_rows;
+    const void* radii;
+    uint64_t sparse_offset_floats;   /* multiple of 4 */
+    uint64_t vis_offset_bytes;       /* multiple of 4 */
 } B200sPeerReduceArgs;
 size_t b200s_peer_allreduce_flag_bytes(int32_t ctas, int32_t world);
+/* rows of the sparse tensor each rank owns (a multiple of the kernel's 1024-row work unit) and the size of
+ * the visibility scratch array (world * rows_per_rank bytes). */
+int64_t b200s_peer_allreduce_rows_per_rank(int32_t rows, int32_t world);
+size_t b200s_peer_allreduce_vis_bytes(int32_t rows, int32_t world);
 int b200s_peer_allreduce_sum_f32(const B200sPeerReduceArgs* args, b200s_stream_t stream);
 
 /* sizeof() of the ABI structs as compiled: 0 B200sHeader, 1 B200sForwardArgs,

@@ -85,7 +85,8 @@ class PeerReduceArgs(C.Structure):
         ("peer_bufs", C.c_void_p * MAX_PEERS), ("peer_flags", C.c_void_p * MAX_PEERS),
         ("multicast_buf", C.c_void_p), ("n_floats", C.c_uint64),
         ("rank", C.c_int32), ("world", C.c_int32), ("epoch", C.c_uint32), ("ctas", C.c_int32),
-        ("use_multimem", C.c_int32), ("reserved", C.c_int32),
+        ("use_multimem", C.c_int32), ("sparse_rows", C.c_int32),
+        ("radii", C.c_void_p), ("sparse_offset_floats", C.c_uint64), ("vis_offset_bytes", C.c_uint64),
     ]
 
 
@@ -129,6 +130,8 @@ SYMBOLS = [
     ("b200s_launch_count", C.c_uint64, []),
     ("b200s_count_pairs", C.c_int, [C.POINTER(ForwardArgs), C.c_void_p, C.c_void_p]),
     ("b200s_peer_allreduce_flag_bytes", C.c_size_t, [C.c_int32, C.c_int32]),
+    ("b200s_peer_allreduce_rows_per_rank", C.c_int64, [C.c_int32, C.c_int32]),
+    ("b200s_peer_allreduce_vis_bytes", C.c_size_t, [C.c_int32, C.c_int32]),
     ("b200s_peer_allreduce_sum_f32", C.c_int, [C.POINTER(PeerReduceArgs), C.c_void_p]),
     ("b200s_export_state", C.c_int64, [C.POINTER(ForwardArgs), C.c_int32, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
 ]

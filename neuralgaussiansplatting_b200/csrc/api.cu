@@ -360,12 +360,26 @@ extern "C" size_t b200s_peer_allreduce_flag_bytes(int32_t ctas, int32_t world) {
     return (size_t)2 * (size_t)ctas * (size_t)world * sizeof(uint32_t);   // two barrier phases
 }
 
+extern "C" int64_t b200s_peer_allreduce_rows_per_rank(int32_t rows, int32_t world) {
+    if (rows <= 0 || world <= 0) return 0;
+    const int64_t per = ((int64_t)rows + world - 1) / world;
+    return (per + 1023) / 1024 * 1024;
+}
+
+extern "C" size_t b200s_peer_allreduce_vis_bytes(int32_t rows, int32_t world) {
+    return (size_t)b200s_peer_allreduce_rows_per_rank(rows, world) * (size_t)(world > 0 ? world : 0);
+}
+
 extern "C" int b200s_peer_allreduce_sum_f32(const B200sPeerReduceArgs* a, b200s_stream_t stream_) {
     if (!a || a->world < 1 || a->world > B200S_MAX_PEERS || a->rank < 0 || a->rank >= a->world) return B200S_E_BADARG;
     if (a->ctas < 1 || a->ctas > 1024 || (a->n_floats & 3u) || a->epoch == 0) return B200S_E_BADARG;
     if (a->use_multimem && !a->multicast_buf) return B200S_E_BADARG;
     for (int r = 0; r < a->world; ++r)
         if (!a->peer_bufs[r] || !a->peer_flags[r] || ((uintptr_t)a->peer_bufs[r] & 15u)) return B200S_E_BADARG;
+    if (a->radii) {
+        if (a->sparse_rows <= 0 || (a->sparse_offset_floats & 3u) || (a->vis_offset_bytes & 3u)) return B200S_E_BADARG;
+        if (a->sparse_offset_floats + (uint64_t)a->sparse_rows * 48u > a->n_floats) return B200S_E_BADARG;
+    }
     if (a->n_floats == 0 || a->world == 1) return 0;
     return launch_peer_allreduce(*a, (cudaStream_t)stream_);
 }

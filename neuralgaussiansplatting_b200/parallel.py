@@ -218,12 +218,17 @@ class PeerGradientAllReduce:
         self.n_buffers, self.ctas = int(n_buffers), int(ctas)
         self.flag_bytes = -(-int(self._lib.b200s_peer_allreduce_flag_bytes(self.ctas, self.world)) // 256) * 256
         self.buf_bytes = self.n_floats * 4
-        self.mem = PeerMemory(self.flag_bytes + self.n_buffers * self.buf_bytes, self.device, group, backend)
+        self.P, self.sh_coeffs = int(P), int(sh_coeffs)
+        # one visibility byte per Gaussian next to every buffer (sparse tail of the collective, see start())
+        self.vis_bytes = -(-int(self._lib.b200s_peer_allreduce_vis_bytes(self.P, self.world)) // 256) * 256
+        self.slot_bytes = self.buf_bytes + self.vis_bytes
+        self.mem = PeerMemory(self.flag_bytes + self.n_buffers * self.slot_bytes, self.device, group, backend)
         self.mem.local.zero_()
         torch.cuda.synchronize(self.device)
         dist.barrier(group=group)                      # nobody raises a flag before every flag array is zero
         self.multimem = bool(multimem) and self.mem.multicast_ptr != 0
-        self._flat = [self.mem.local[self.flag_bytes + i * self.buf_bytes: self.flag_bytes + (i + 1) * self.buf_bytes]
+        self._flat = [self.mem.local[self.flag_bytes + i * self.slot_bytes:
+                                     self.flag_bytes + i * self.slot_bytes + self.buf_bytes]
                       .view(torch.float32) for i in range(self.n_buffers)]
         self._cur = -1
         self._epoch = 0
@@ -248,7 +253,11 @@ class PeerGradientAllReduce:
         return self._views(self._cur)
 
     # ---- collective
-    def start(self, grads: Optional[Dict[str, torch.Tensor]] = None) -> None:
+    def start(self, grads: Optional[Dict[str, torch.Tensor]] = None, radii: Optional[torch.Tensor] = None) -> None:
+        """Launch the collective for the current buffer. `radii` (int32[P], this rank's forward output for the
+        view the gradients belong to) enables the visibility-sparse SH tail: rows with radii <= 0 are all-zero
+        here, so owners skip them — same bits as the dense sum, less NVLink traffic. Only pass it when the
+        buffer holds the gradients of exactly that one view (not a local accumulation over several views)."""
         if self._cur < 0:
             self._cur = 0
         views = self._views(self._cur)
@@ -261,7 +270,15 @@ class PeerGradientAllReduce:
                     views[k].copy_(g.reshape(views[k].shape))
                 self._copy_back = (stray, views)
         a = self._libmod.PeerReduceArgs()
-        off = self.flag_bytes + self._cur * self.buf_bytes
+        off = self.flag_bytes + self._cur * self.slot_bytes
+        if radii is not None and self.sh_coeffs == 16 and not self.multimem and self._copy_back is None:
+            if radii.dtype != torch.int32 or radii.numel() != self.P or not radii.is_cuda or not radii.is_contiguous():
+                raise ValueError("radii must be a contiguous int32 CUDA tensor with one entry per Gaussian")
+            a.radii = radii.data_ptr()
+            a.sparse_rows = self.P
+            a.sparse_offset_floats = self.layout["shs"][0]
+            a.vis_offset_bytes = self.buf_bytes
+            self._radii_keep = radii
         for r in range(self.world):
             a.peer_bufs[r] = self.mem.ptrs[r] + off
             a.peer_flags[r] = self.mem.ptrs[r]

@@ -40,7 +40,8 @@ def test_abi_version_and_build_info(lib):
 
 
 def test_struct_layouts_match(lib):
-    for which, st in enumerate((_lib.Header, _lib.ForwardArgs, _lib.BackwardArgs, _lib.IdxmapArgs)):
+    for which, st in enumerate((_lib.Header, _lib.ForwardArgs, _lib.BackwardArgs, _lib.IdxmapArgs,
+                                _lib.PeerReduceArgs)):
         assert lib.b200s_sizeof(which) == C.sizeof(st)
     assert C.sizeof(_lib.Header) == 64
     assert lib.b200s_sizeof(99) == 0
@@ -94,6 +95,27 @@ def test_argument_errors_without_a_device(lib):
     assert lib.b200s_mark_visible(0, None, None, None, None, None) == 0
     assert lib.b200s_idxmap_backward(-1, 4, 4, None, None, None, None) == -1
     assert lib.b200s_read_header(None, None, None) == -1
+
+
+def test_peer_allreduce_argument_checks(lib):
+    assert lib.b200s_peer_allreduce_flag_bytes(32, 8) == 2 * 32 * 8 * 4
+    assert lib.b200s_peer_allreduce_flag_bytes(0, 8) == 0
+    assert lib.b200s_peer_allreduce_sum_f32(None, None) == -1
+    a = _lib.PeerReduceArgs()
+    a.rank, a.world, a.ctas, a.epoch, a.n_floats = 0, 2, 16, 1, 1024
+    assert lib.b200s_peer_allreduce_sum_f32(C.byref(a), None) == -1      # NULL peer buffers
+    a.peer_bufs[0] = a.peer_bufs[1] = 4096
+    a.peer_flags[0] = a.peer_flags[1] = 8192
+    a.n_floats = 1022
+    assert lib.b200s_peer_allreduce_sum_f32(C.byref(a), None) == -1      # not a multiple of 4 floats
+    a.n_floats, a.epoch = 1024, 0
+    assert lib.b200s_peer_allreduce_sum_f32(C.byref(a), None) == -1      # epochs start at 1
+    a.epoch, a.rank = 1, 2
+    assert lib.b200s_peer_allreduce_sum_f32(C.byref(a), None) == -1      # rank outside the world
+    a.rank, a.use_multimem = 0, 1
+    assert lib.b200s_peer_allreduce_sum_f32(C.byref(a), None) == -1      # multimem without a multicast mapping
+    a.use_multimem, a.world = 0, 1
+    assert lib.b200s_peer_allreduce_sum_f32(C.byref(a), None) == 0       # world of one: nothing to do, no launch
 
 
 def test_check_turns_status_into_runtime_error():

@@ -2,6 +2,7 @@
 render() caller, the equivalence relations the reference's own pipeline toggles define
 (gaussian_renderer/__init__.py:63-81), the idxmap extra channels against the reference rasterizer2, and the
 committed golden vectors."""
+import json
 import math
 from pathlib import Path
 
@@ -200,3 +201,20 @@ def test_cuda_path_matches_committed_reference_golden(dev, variant):
     names = ["means2D", "opacity", "means3D", "colors", "cov3D"] + ([] if pre else ["sh", "scales", "rotations"])
     for k in names:
         assert Hh.rel_l2(grads[k].cpu().reshape(g["g_" + k].shape), torch.from_numpy(g["g_" + k])) < 1e-4, k
+
+
+@pytest.mark.gpu
+def test_peer_allreduce_two_ranks_exact():
+    """b200s_peer_allreduce_sum_f32 over NVLink peer memory, 2 ranks: exact fixed-order sum, identical replicas,
+    copy path for non-aliasing gradients (tools/peer_check.py --quick). Needs two GPUs on the box."""
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533", str(root / "tools" / "peer_check.py"),
+                        "--quick"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    rep = json.loads(r.stdout.strip().splitlines()[-1])
+    assert rep["stray_copy_path"] and all(rep[f"small_trial{i}"]["exact_fixed_order_sum"] for i in range(3))

@@ -40,6 +40,24 @@ def test_buckets_cover_every_element_once():
     assert all(float(v.min()) == 1.0 and float(v.max()) == 1.0 for v in g.values())   # views, not copies
 
 
+def test_gradient_layout_is_aligned_and_disjoint():
+    for P in (1, 7, 257, 10_007, 3_000_000):
+        lay, total = par.gradient_layout(P, 16)
+        assert total % 64 == 0 and set(lay) == set(par.PARAM_ORDER)
+        spans = []
+        for name, (off, shape) in lay.items():
+            n = 1
+            for d in shape:
+                n *= d
+            assert off % 64 == 0                       # 256-byte aligned sub-tensors (16-byte vector stores)
+            spans.append((off, off + n))
+        spans.sort()
+        assert all(a[1] <= b[0] for a, b in zip(spans, spans[1:])) and spans[-1][1] <= total
+        assert sum(b - a for a, b in spans) == P * par.GRAD_FLOATS_PER_GAUSSIAN
+    lay, total = par.gradient_layout(3_000_000)
+    assert total * 4 == par.allreduce_payload_bytes(3_000_000)     # no padding at the bench size
+
+
 def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
 

@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--P", type=int, default=3_000_000)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--backend", default="auto")
+    ap.add_argument("--quick", action="store_true", help="exactness checks only")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -52,6 +53,29 @@ def main():
         same = all(torch.equal(allf[0], x) for x in allf[1:])
         report[f"small_trial{trial}"] = {"exact_fixed_order_sum": exact, "replicas_identical": same}
         assert exact and same, report
+    # visibility-sparse tail: rows with radii <= 0 are zero on that rank; result must equal the dense fixed-order sum
+    for trial in range(3):
+        views = small.grad_out()
+        g = torch.Generator(device=dev).manual_seed(1000 + 100 * trial + rank)
+        radii = (torch.rand(10_007, device=dev, generator=g) < (0.43 if trial < 2 else 0.02)).to(torch.int32) * 7
+        for v in views.values():
+            v.copy_(torch.randn(v.shape, device=dev, generator=g))
+            v[radii <= 0] = 0.0
+        flat = small._flat[small._cur]
+        gathered = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat.clone())
+        expect = gathered[0].clone()
+        for r in range(1, world):
+            expect += gathered[r]
+        small.start(views, radii=radii)
+        small.wait()
+        torch.cuda.synchronize()
+        exact = bool(torch.equal(flat, expect))
+        allf = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(allf, flat)
+        same = all(torch.equal(allf[0], x) for x in allf[1:])
+        report[f"sparse_trial{trial}"] = {"equals_dense_fixed_order_sum": exact, "replicas_identical": same}
+        assert exact and same, report
     # stray (non-aliasing) gradients are copied in and back
     stray = {k: torch.full(v.shape, float(rank + 1), device=dev) for k, v in small._views(0).items()}
     small.grad_out()
@@ -62,6 +86,11 @@ def main():
     assert all(bool((v == tot).all()) for v in stray.values())
     report["stray_copy_path"] = True
     del small
+    if a.quick:
+        if rank == 0:
+            print(json.dumps(report))
+        dist.destroy_process_group()
+        return
 
     # ---- timing at the bench payload
     def time_it(fn, iters):
@@ -80,18 +109,26 @@ def main():
     layout, n_floats = parallel.gradient_layout(a.P)
     nbytes = n_floats * 4
     times = {}
-    for mm in (False, True):
-        for ctas in (8, 16, 32, 64):
-            red = parallel.PeerGradientAllReduce(a.P, 16, dev, ctas=ctas, multimem=mm, n_buffers=1, backend=a.backend)
-            if mm and not red.multimem:
+    g = torch.Generator(device=dev).manual_seed(7 + rank)
+    radii43 = (torch.rand(a.P, device=dev, generator=g) < 0.43).to(torch.int32)
+    for mm in (False, "sparse", True):
+        for ctas in (8, 16, 32):
+            red = parallel.PeerGradientAllReduce(a.P, 16, dev, ctas=ctas, multimem=(mm is True), n_buffers=1,
+                                                 backend=a.backend)
+            if mm is True and not red.multimem:
                 del red
                 break
-            red.grad_out()
+            views = red.grad_out()
+            rad = None
+            if mm == "sparse":
+                rad = radii43
+                for v in views.values():
+                    v[rad <= 0] = 0.0
 
             def fn():
-                red.start(None); red.wait()
+                red.start(None, radii=rad); red.wait()
             ms = time_it(fn, a.iters)
-            times[f"{'multimem' if mm else 'p2p'}_ctas{ctas}"] = {"ms": round(ms, 4), "algbw_GBps": round(nbytes / ms / 1e6, 1)}
+            times[f"{'multimem' if mm is True else 'sparse43' if mm else 'p2p'}_ctas{ctas}"] = {"ms": round(ms, 4), "algbw_GBps": round(nbytes / ms / 1e6, 1)}
             del red
             torch.cuda.empty_cache()
     x = torch.zeros(n_floats, device=dev)
