@@ -210,7 +210,7 @@ def run_ours(args, rank, local_rank, world, dev):
             _C.config["grad_out"] = reducer.grad_out
             collective_kind = (f"b200s_peer_allreduce_sum_f32 ({'multimem/NVLS' if reducer.multimem else 'P2P two-shot'}, "
                                f"{reducer.ctas} CTAs, {reducer.mem.backend} mappings"
-                               + ("" if args.dense_collective or reducer.multimem else
+                               + ("" if not args.sparse_collective or reducer.multimem else
                                   ", dL/dSH rows read only from ranks whose view saw the Gaussian (radii > 0)") + ")")
         else:
             reducer = parallel.GradientAllReduce()
@@ -219,7 +219,7 @@ def run_ours(args, rank, local_rank, world, dev):
 
     overlap = args.allreduce == "overlap"
 
-    sparse = world > 1 and args.collective == "peer" and not args.dense_collective
+    sparse = world > 1 and args.collective == "peer" and args.sparse_collective
 
     def reduce_step(grads, radii=None):
         if reducer is None:
@@ -547,9 +547,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1, our arm: gradient all-reduce as the library's own NVLink peer-memory kernel, or NCCL")
-    ap.add_argument("--peer-ctas", type=int, default=16)
-    ap.add_argument("--dense-collective", action="store_true",
-                    help="peer collective: do not use the view's radii to skip all-zero dL/dSH rows")
+    ap.add_argument("--peer-ctas", type=int, default=0, help="0 = per-world-size default (16 / 12 / 8 at 2 / 4 / 8)")
+    ap.add_argument("--sparse-collective", action="store_true",
+                    help="peer collective: use the view's radii to skip all-zero dL/dSH rows (exact; fewer NVLink "
+                         "bytes but fewer loads in flight per CTA — slower at 2 GPUs, see DESIGN.md §7)")
     ap.add_argument("--multimem", action="store_true", help="peer collective: NVSwitch multimem.ld_reduce/st")
     ap.add_argument("--allreduce", default="overlap", choices=["overlap", "blocking"],
                     help="N>1: overlap the gradient all-reduce of view k with the rasterization of view k+1")

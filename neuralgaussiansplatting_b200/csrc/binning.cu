@@ -287,6 +287,10 @@ sort_scan_hist_kernel(uint32_t* hist) {
     h[tid] = wex + incl - c;
 }
 
+#ifndef B200S_SORT_MINB
+#define B200S_SORT_MINB 3
+#endif
+constexpr int SORT_MINB = B200S_SORT_MINB;   // resident CTAs per SM requested from ptxas (register cap)
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr int SORT_CNT_STRIDE = SORT_RADIX + 1;      // + sentinel digit for padding items
 constexpr size_t SORT_SMEM = (size_t)SORT_TILE * 4 + (size_t)SORT_TILE * 4 +
@@ -296,7 +300,7 @@ constexpr size_t SORT_SMEM = (size_t)SORT_TILE * 4 + (size_t)SORT_TILE * 4 +
 // blocks ("onesweep"), in-block ranking by warp match. `n` is read from device memory; a count
 // above `capacity` (binning overflow) makes the pass a no-op.
 template <bool USE_MATCH>
-__global__ void __launch_bounds__(SORT_THREADS)
+__global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
 sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                      B200sHeader* header, const uint32_t* __restrict__ n_ptr, int64_t capacity, int shift,

@@ -25,10 +25,11 @@ namespace b200s {
 constexpr float ALPHA_MIN_B = BLEND_ALPHA_MIN;
 
 // Sum of nine per-lane partials over the warp. The first eight are reduced with a transposing
-// butterfly (4 + 2 + 1 + 1 + 1 = 9 shuffles instead of 40): after it lane l holds the warp total
-// of value ((l >> 4) & 1) * 4 + ((l >> 3) & 1) * 2 + ((l >> 2) & 1). The ninth takes the plain
-// five steps. Returns this lane's value and its index in `which` (-1: nothing to write; only
-// lanes 0, 4, .., 28 and lane 1 — which carries the ninth — write).
+// butterfly (4 + 2 + 1 shuffles leave lane l with the sum, over the lanes that differ from it in
+// bits 4..2, of value ((l >> 4) & 1) * 4 + ((l >> 3) & 1) * 2 + ((l >> 2) & 1)); the ninth takes
+// the plain steps 16, 8, 4; the last two steps (2, 1) finish both at once, the ninth riding in the
+// lanes with bit 1 set: 12 shuffles instead of 45. Returns this lane's value and its index in
+// `which` (-1: nothing to write; lanes 0, 4, .., 28 write values 0..7, lane 2 writes the ninth).
 __device__ __forceinline__ float reduce9(float (&acc)[9], int lane, int& which) {
     {
         const bool hi = lane & 16;
@@ -54,14 +55,17 @@ __device__ __forceinline__ float reduce9(float (&acc)[9], int lane, int& which) 
         const float keep = hi ? acc[1] : acc[0];
         acc[0] = keep + __shfl_xor_sync(FULL_MASK, send, 4);
     }
-    acc[0] += __shfl_xor_sync(FULL_MASK, acc[0], 2);
-    acc[0] += __shfl_xor_sync(FULL_MASK, acc[0], 1);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc[8] += __shfl_xor_sync(FULL_MASK, acc[8], o);
+    for (int o = 16; o >= 4; o >>= 1) acc[8] += __shfl_xor_sync(FULL_MASK, acc[8], o);
+    const bool hi = lane & 2;
+    const float send = hi ? acc[0] : acc[8];
+    const float keep = hi ? acc[8] : acc[0];
+    float r = keep + __shfl_xor_sync(FULL_MASK, send, 2);
+    r += __shfl_xor_sync(FULL_MASK, r, 1);
     which = -1;
     if ((lane & 3) == 0) which = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-    if (lane == 1) which = 8;
-    return lane == 1 ? acc[8] : acc[0];
+    if (lane == 2) which = 8;
+    return r;
 }
 
 template <int NW, int SPT>
@@ -279,6 +283,9 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
                     const float power = ffma(sq, -0.5f, -fmul(dy[iy], bx[ix]));
                     if (lpos >= lastc[s]) continue;          // behind this pixel's last contributor
                     if (power > 0.0f || power < Q.y) continue;
+                    // Same accurate expf as the forward: T is recovered by dividing by (1 - alpha), which
+                    // amplifies any mismatch with the forward's alpha by alpha / (1 - alpha) (up to 99x), so a
+                    // MUFU.EX2-only G (2^-22 relative error) costs 2.4e-4 rel-L2 on dL/dopacity (measured, C1).
                     const float G = expf(power);
                     const float alpha = fminf(0.99f, fmul(B.y, G));
                     if (alpha < ALPHA_MIN_B) continue;
@@ -290,11 +297,14 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
                     acc[0] += wgt * gr[s];
                     acc[1] += wgt * gg[s];
                     acc[2] += wgt * gb[s];
-                    float dL_dalpha = ((B.z - Ar[s]) * gr[s] + (B.w - Ag[s]) * gg[s] + (Q.x - Ab[s]) * gb[s]) * T[s];
+                    // c - accumulated colour behind this Gaussian, per channel (backward.cu:505-512); the same
+                    // differences update the accumulators: A += alpha * (c - A)  ==  alpha*c + (1-alpha)*A
+                    const float dr_ = B.z - Ar[s], dg_ = B.w - Ag[s], db_ = Q.x - Ab[s];
+                    float dL_dalpha = (dr_ * gr[s] + dg_ * gg[s] + db_ * gb[s]) * T[s];
                     dL_dalpha += Tf_bg[s] * inv;
-                    Ar[s] = alpha * B.z + one_m * Ar[s];
-                    Ag[s] = alpha * B.w + one_m * Ag[s];
-                    Ab[s] = alpha * Q.x + one_m * Ab[s];
+                    Ar[s] = fmaf(alpha, dr_, Ar[s]);
+                    Ag[s] = fmaf(alpha, dg_, Ag[s]);
+                    Ab[s] = fmaf(alpha, db_, Ab[s]);
                     const float gda = G * dL_dalpha;
                     const float u = B.y * gda;
                     const float udx = u * dx[ix], udy = u * dy[iy];

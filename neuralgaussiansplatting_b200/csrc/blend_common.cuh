@@ -67,6 +67,13 @@ __device__ __forceinline__ float rcp_approx(float x) {
     return r;
 }
 
+constexpr float LOG2E_F = 1.4426950408889634f;
+__device__ __forceinline__ float ex2_approx(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 // Per-Gaussian constants of the rectangle test.
 struct ReachCtx {
     float x, y, a, b, c;

@@ -204,7 +204,12 @@ class PeerGradientAllReduce:
     Same start()/wait() protocol as GradientAllReduce. Gradients that do not alias the current buffer (autograd
     cloned them) are copied in and back out."""
 
-    def __init__(self, P: int, sh_coeffs: int = 16, device=None, group=None, n_buffers: int = 2, ctas: int = 32,
+    # CTAs of 512 threads that saturate NVLink per world size (measured on 8x B200, tools/peer_check.py): each
+    # thread keeps 16 loads in flight of which (world-1)/world are remote; more CTAs only take SMs from the
+    # rasterizer that runs concurrently.
+    AUTO_CTAS = {2: 16, 3: 16, 4: 12}
+
+    def __init__(self, P: int, sh_coeffs: int = 16, device=None, group=None, n_buffers: int = 2, ctas: int = 0,
                  multimem: bool = False, backend: str = "auto"):
         from . import _lib
         self._libmod = _lib
@@ -215,7 +220,8 @@ class PeerGradientAllReduce:
             raise ValueError(f"at most {_lib.MAX_PEERS} peers")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.layout, self.n_floats = gradient_layout(P, sh_coeffs)
-        self.n_buffers, self.ctas = int(n_buffers), int(ctas)
+        self.n_buffers = int(n_buffers)
+        self.ctas = int(ctas) if ctas and ctas > 0 else self.AUTO_CTAS.get(self.world, 8)
         self.flag_bytes = -(-int(self._lib.b200s_peer_allreduce_flag_bytes(self.ctas, self.world)) // 256) * 256
         self.buf_bytes = self.n_floats * 4
         self.P, self.sh_coeffs = int(P), int(sh_coeffs)
