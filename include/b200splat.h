@@ -290,8 +290,52 @@ int64_t b200s_peer_allreduce_rows_per_rank(int32_t rows, int32_t world);
 size_t b200s_peer_allreduce_vis_bytes(int32_t rows, int32_t world);
 int b200s_peer_allreduce_sum_f32(const B200sPeerReduceArgs* args, b200s_stream_t stream);
 
+/* ---- fused activation-backward + Adam + activation-forward for the replicated Gaussian
+ *      parameters. Replaces, for the Gaussian tensors, autograd's chain
+ *      through get_opacity / get_scaling / get_rotation / get_features (scene/gaussian_model.py:113-141),
+ *      torch.optim.Adam(l, lr=0.0, eps=1e-15).step() over the param groups of training_setup
+ *      (scene/gaussian_model.py:252-279, train.py:127-128) and the next iteration's activations
+ *      + torch.cat. One launch over up to B200S_ADAM_MAX_TENSORS tensors, all float32, 16-byte
+ *      aligned, updated in place. `grad` is dL/d(ACTIVATED value) exactly as b200s_backward emits it
+ *      (after the all-reduce); `activated` receives activation(param_new) for the next forward (NULL
+ *      or == param: not written). Adam arithmetic follows torch's single-tensor path operation by
+ *      operation: m.lerp_(g, 1-b1); v.mul_(b2).addcmul_(g, g, 1-b2); denom = sqrt(v)/bc2_sqrt + eps;
+ *      p.addcdiv_(m, denom, -step_size), with step_size = lr / (1 - b1^t) computed by the caller in
+ *      double (as torch does) and passed negated. */
+#define B200S_ADAM_MAX_TENSORS 8
+enum {
+    B200S_ADAM_IDENTITY = 0,   /* xyz */
+    B200S_ADAM_SH = 1,         /* [P,16,3]: coefficient 0 steps with neg_step (f_dc), 1..15 with neg_step_rest (f_rest) */
+    B200S_ADAM_EXP = 2,        /* scaling */
+    B200S_ADAM_SIGMOID = 3,    /* opacity */
+    B200S_ADAM_NORMALIZE = 4   /* rotation, rows of 4 (torch.nn.functional.normalize, eps 1e-12) */
+};
+typedef struct B200sAdamTensor {
+    float* param;              /* raw (pre-activation) parameter */
+    float* exp_avg;
+    float* exp_avg_sq;
+    const float* grad;         /* dL/d activated */
+    float* activated;          /* out: activation(param) after the update, or NULL */
+    int64_t n;                 /* floats (SH: multiple of 48, NORMALIZE: multiple of 4) */
+    float neg_step;            /* -(lr / bias_correction1) */
+    float neg_step_rest;       /* SH only */
+    int32_t mode;
+    int32_t reserved;
+} B200sAdamTensor;
+typedef struct B200sAdamArgs {
+    B200sAdamTensor t[B200S_ADAM_MAX_TENSORS];
+    int32_t count;
+    float beta1, beta2;
+    float one_minus_beta1, one_minus_beta2;   /* float(1 - beta) computed in double, as torch passes them */
+    float eps;
+    float bias_correction2_sqrt;               /* sqrt(1 - beta2^step) */
+    int32_t reserved;
+} B200sAdamArgs;
+int b200s_adam_step(const B200sAdamArgs* args, b200s_stream_t stream);
+
 /* sizeof() of the ABI structs as compiled: 0 B200sHeader, 1 B200sForwardArgs,
- * 2 B200sBackwardArgs, 3 B200sIdxmapArgs, 4 B200sPeerReduceArgs. Bindings assert their own layout against it. */
+ * 2 B200sBackwardArgs, 3 B200sIdxmapArgs, 4 B200sPeerReduceArgs,
+ * 5 B200sAdamArgs. Bindings assert their own layout against it. */
 size_t b200s_sizeof(int32_t which);
 
 /* Library / build identification. */

@@ -90,6 +90,26 @@ class PeerReduceArgs(C.Structure):
     ]
 
 
+ADAM_MAX_TENSORS = 8
+ADAM_MODES = {"identity": 0, "sh": 1, "exp": 2, "sigmoid": 3, "normalize": 4}
+
+
+class AdamTensor(C.Structure):
+    _fields_ = [
+        ("param", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p), ("grad", C.c_void_p),
+        ("activated", C.c_void_p), ("n", C.c_int64), ("neg_step", C.c_float), ("neg_step_rest", C.c_float),
+        ("mode", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class AdamArgs(C.Structure):
+    _fields_ = [
+        ("t", AdamTensor * ADAM_MAX_TENSORS), ("count", C.c_int32), ("beta1", C.c_float), ("beta2", C.c_float),
+        ("one_minus_beta1", C.c_float), ("one_minus_beta2", C.c_float), ("eps", C.c_float),
+        ("bias_correction2_sqrt", C.c_float), ("reserved", C.c_int32),
+    ]
+
+
 STATE = {
     "depths": 0, "means2D": 1, "conic_opacity": 2, "rgb": 3, "tiles_touched": 4, "point_offsets": 5,
     "point_list": 6, "point_list_keys": 7, "ranges": 8, "n_contrib": 9, "final_T": 10, "clamped": 11,
@@ -133,6 +153,7 @@ SYMBOLS = [
     ("b200s_peer_allreduce_rows_per_rank", C.c_int64, [C.c_int32, C.c_int32]),
     ("b200s_peer_allreduce_vis_bytes", C.c_size_t, [C.c_int32, C.c_int32]),
     ("b200s_peer_allreduce_sum_f32", C.c_int, [C.POINTER(PeerReduceArgs), C.c_void_p]),
+    ("b200s_adam_step", C.c_int, [C.POINTER(AdamArgs), C.c_void_p]),
     ("b200s_export_state", C.c_int64, [C.POINTER(ForwardArgs), C.c_int32, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
 ]
 
@@ -162,7 +183,7 @@ def load() -> C.CDLL:
         fn.argtypes = argtypes
     if lib.b200s_abi_version() != 1:
         raise RuntimeError("libb200splat.so ABI version mismatch")
-    for which, struct in enumerate((Header, ForwardArgs, BackwardArgs, IdxmapArgs, PeerReduceArgs)):
+    for which, struct in enumerate((Header, ForwardArgs, BackwardArgs, IdxmapArgs, PeerReduceArgs, AdamArgs)):
         if lib.b200s_sizeof(which) != C.sizeof(struct):
             raise RuntimeError(f"ctypes layout of {struct.__name__} does not match the library")
     _lib = lib

@@ -168,6 +168,7 @@ size_t b200s_sizeof(int32_t which) {
         case 2: return sizeof(B200sBackwardArgs);
         case 3: return sizeof(B200sIdxmapArgs);
         case 4: return sizeof(B200sPeerReduceArgs);
+        case 5: return sizeof(B200sAdamArgs);
         default: return 0;
     }
 }
@@ -382,6 +383,22 @@ extern "C" int b200s_peer_allreduce_sum_f32(const B200sPeerReduceArgs* a, b200s_
     }
     if (a->n_floats == 0 || a->world == 1) return 0;
     return launch_peer_allreduce(*a, (cudaStream_t)stream_);
+}
+
+extern "C" int b200s_adam_step(const B200sAdamArgs* a, b200s_stream_t stream_) {
+    if (!a || a->count < 0 || a->count > B200S_ADAM_MAX_TENSORS) return B200S_E_BADARG;
+    if (!(a->bias_correction2_sqrt > 0.0f)) return B200S_E_BADARG;
+    for (int i = 0; i < a->count; ++i) {
+        const B200sAdamTensor& t = a->t[i];
+        if (t.n < 0 || t.mode < B200S_ADAM_IDENTITY || t.mode > B200S_ADAM_NORMALIZE) return B200S_E_BADARG;
+        if (t.n == 0) continue;
+        if (!t.param || !t.exp_avg || !t.exp_avg_sq || !t.grad) return B200S_E_BADARG;
+        if (((uintptr_t)t.param | (uintptr_t)t.exp_avg | (uintptr_t)t.exp_avg_sq | (uintptr_t)t.grad |
+             (uintptr_t)t.activated) & 15u) return B200S_E_BADARG;
+        if (t.mode == B200S_ADAM_SH && t.n % 48) return B200S_E_BADARG;
+        if (t.mode == B200S_ADAM_NORMALIZE && t.n % 4) return B200S_E_BADARG;
+    }
+    return launch_adam_step(*a, (cudaStream_t)stream_);
 }
 
 extern "C" int b200s_count_pairs(const B200sForwardArgs* a, unsigned long long* counts_dev, b200s_stream_t stream_) {

@@ -106,5 +106,6 @@ int launch_blend_fwd(const BlendFwdParams& p, int nw, cudaStream_t stream);
 int launch_blend_bwd(const BlendBwdParams& p, int nw, cudaStream_t stream);
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream);
 int launch_peer_allreduce(const B200sPeerReduceArgs& a, cudaStream_t stream);
+int launch_adam_step(const B200sAdamArgs& a, cudaStream_t stream);
 
 }  // namespace b200s
