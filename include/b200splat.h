@@ -333,9 +333,31 @@ typedef struct B200sAdamArgs {
 } B200sAdamArgs;
 int b200s_adam_step(const B200sAdamArgs* args, b200s_stream_t stream);
 
+/* ---- fused photometric loss: value and gradient of
+ *      (1 - lambda_dssim) * l1_loss(image, gt) + lambda_dssim * (1 - ssim(image, gt))
+ *      as train.py:91-92 forms it from utils/loss_utils.py:17-18 (l1_loss) and :27-63 (gaussian,
+ *      create_window, ssim, _ssim: 11x11 window, sigma 1.5, zero padding 5, C1 = 0.01^2, C2 = 0.03^2,
+ *      mean over all C*H*W). image, gt: [C,H,W] float32. loss_out: float[3] = {loss, l1, ssim}.
+ *      dL_dimage: [C,H,W] = grad_scale * dloss/dimage, or NULL for the value only. ws: scratch of
+ *      b200s_loss_workspace_size bytes (three derivative maps + per-block partial sums, which are added in
+ *      index order: the value is reproducible run to run). */
+typedef struct B200sLossArgs {
+    int32_t C, H, W;
+    float lambda_dssim;
+    float grad_scale;            /* upstream dL/dloss (1 for loss.backward()) */
+    int32_t reserved;
+    const float* image;
+    const float* gt;
+    float* loss_out;
+    float* dL_dimage;
+    void* ws; size_t ws_bytes;
+} B200sLossArgs;
+size_t b200s_loss_workspace_size(int32_t C, int32_t H, int32_t W);
+int b200s_l1_ssim_loss(const B200sLossArgs* args, b200s_stream_t stream);
+
 /* sizeof() of the ABI structs as compiled: 0 B200sHeader, 1 B200sForwardArgs,
  * 2 B200sBackwardArgs, 3 B200sIdxmapArgs, 4 B200sPeerReduceArgs,
- * 5 B200sAdamArgs. Bindings assert their own layout against it. */
+ * 5 B200sAdamArgs, 6 B200sLossArgs. Bindings assert their own layout against it. */
 size_t b200s_sizeof(int32_t which);
 
 /* Library / build identification. */

@@ -110,6 +110,14 @@ class AdamArgs(C.Structure):
     ]
 
 
+class LossArgs(C.Structure):
+    _fields_ = [
+        ("C", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("lambda_dssim", C.c_float), ("grad_scale", C.c_float),
+        ("reserved", C.c_int32), ("image", C.c_void_p), ("gt", C.c_void_p), ("loss_out", C.c_void_p),
+        ("dL_dimage", C.c_void_p), ("ws", C.c_void_p), ("ws_bytes", C.c_size_t),
+    ]
+
+
 STATE = {
     "depths": 0, "means2D": 1, "conic_opacity": 2, "rgb": 3, "tiles_touched": 4, "point_offsets": 5,
     "point_list": 6, "point_list_keys": 7, "ranges": 8, "n_contrib": 9, "final_T": 10, "clamped": 11,
@@ -154,6 +162,8 @@ SYMBOLS = [
     ("b200s_peer_allreduce_vis_bytes", C.c_size_t, [C.c_int32, C.c_int32]),
     ("b200s_peer_allreduce_sum_f32", C.c_int, [C.POINTER(PeerReduceArgs), C.c_void_p]),
     ("b200s_adam_step", C.c_int, [C.POINTER(AdamArgs), C.c_void_p]),
+    ("b200s_loss_workspace_size", C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
+    ("b200s_l1_ssim_loss", C.c_int, [C.POINTER(LossArgs), C.c_void_p]),
     ("b200s_export_state", C.c_int64, [C.POINTER(ForwardArgs), C.c_int32, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
 ]
 
@@ -183,7 +193,7 @@ def load() -> C.CDLL:
         fn.argtypes = argtypes
     if lib.b200s_abi_version() != 1:
         raise RuntimeError("libb200splat.so ABI version mismatch")
-    for which, struct in enumerate((Header, ForwardArgs, BackwardArgs, IdxmapArgs, PeerReduceArgs, AdamArgs)):
+    for which, struct in enumerate((Header, ForwardArgs, BackwardArgs, IdxmapArgs, PeerReduceArgs, AdamArgs, LossArgs)):
         if lib.b200s_sizeof(which) != C.sizeof(struct):
             raise RuntimeError(f"ctypes layout of {struct.__name__} does not match the library")
     _lib = lib

@@ -169,6 +169,7 @@ size_t b200s_sizeof(int32_t which) {
         case 3: return sizeof(B200sIdxmapArgs);
         case 4: return sizeof(B200sPeerReduceArgs);
         case 5: return sizeof(B200sAdamArgs);
+        case 6: return sizeof(B200sLossArgs);
         default: return 0;
     }
 }
@@ -399,6 +400,18 @@ extern "C" int b200s_adam_step(const B200sAdamArgs* a, b200s_stream_t stream_) {
         if (t.mode == B200S_ADAM_NORMALIZE && t.n % 4) return B200S_E_BADARG;
     }
     return launch_adam_step(*a, (cudaStream_t)stream_);
+}
+
+extern "C" size_t b200s_loss_workspace_size(int32_t C_, int32_t H, int32_t W) {
+    if (C_ <= 0 || H <= 0 || W <= 0) return 0;
+    return loss_workspace_size(C_, H, W);
+}
+
+extern "C" int b200s_l1_ssim_loss(const B200sLossArgs* a, b200s_stream_t stream_) {
+    if (!a || a->C <= 0 || a->H <= 0 || a->W <= 0) return B200S_E_BADARG;
+    if (!a->image || !a->gt || !a->loss_out || !a->ws) return B200S_E_BADARG;
+    if (a->ws_bytes < loss_workspace_size(a->C, a->H, a->W)) return B200S_E_WORKSPACE;
+    return launch_l1_ssim(*a, (cudaStream_t)stream_);
 }
 
 extern "C" int b200s_count_pairs(const B200sForwardArgs* a, unsigned long long* counts_dev, b200s_stream_t stream_) {

@@ -107,5 +107,7 @@ int launch_blend_bwd(const BlendBwdParams& p, int nw, cudaStream_t stream);
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream);
 int launch_peer_allreduce(const B200sPeerReduceArgs& a, cudaStream_t stream);
 int launch_adam_step(const B200sAdamArgs& a, cudaStream_t stream);
+size_t loss_workspace_size(int C, int H, int W);
+int launch_l1_ssim(const B200sLossArgs& a, cudaStream_t stream);
 
 }  // namespace b200s
