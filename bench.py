@@ -333,11 +333,110 @@ def run_ours(args, rank, local_rank, world, dev):
         "gpu_launches": launches,
         "clocks": clk.summary(),
     }
+    if world == 1:
+        out["full_iteration"] = full_iteration_ours(args, w, _C, dev)
     if rank == 0:
         out.update(roofline_pass(args, w, lib, _C, lambda s: step_resident(s, collective=False)))
         if not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(w)
     return out
+
+
+def full_iteration_ours(args, w, _C, dev):
+    """One whole training iteration with this repo's kernels either side of the rasterizer (SURVEY.md §8(f) ranks
+    2-3): forward -> fused L1+SSIM loss and dL/dimage (loss.py) -> backward -> fused activation-backward + Adam +
+    activation (optimizer.py). Device-resident ground truth; informational, the headline metric stays fwd+bwd."""
+    from neuralgaussiansplatting_b200.loss import fused_l1_ssim
+    from neuralgaussiansplatting_b200.optimizer import FusedGaussianAdam
+    s, cfg = w.scene, w.cfg
+    raw = dict(xyz=s["means3D"].clone(), features=s["shs"].clone(),
+               opacity=torch.logit(s["opacities"].clamp(1e-6, 1 - 1e-6)), scaling=torch.log(s["scales"]),
+               rotation=s["rotations"].clone())
+    opt = FusedGaussianAdam(raw)
+    gts = [t.to(dev) for t in w.gt_host]
+    E = torch.Tensor([])
+
+    def step(i):
+        v = w.view_of(i)
+        c, a = w.cams[v], opt.activated
+        fa = (w.bg, a["means3D"], E, a["opacities"], a["scales"], a["rotations"], 1.0, E, c.world_view_transform,
+              c.full_proj_transform, w.tan[0], w.tan[1], cfg.height, cfg.width, a["shs"], 3, c.camera_center, False,
+              False)
+        out = _C.rasterize_gaussians(*fa)
+        _, dL = fused_l1_ssim(out[1], gts[v], 0.2)
+        g = _C.rasterize_gaussians_backward(fa[0], fa[1], out[2], fa[2], fa[4], fa[5], fa[6], fa[7], fa[8], fa[9],
+                                            fa[10], fa[11], dL, fa[14], fa[15], fa[16], out[3], out[0], out[4],
+                                            out[5], False)
+        opt.step({"means3D": g[3], "opacities": g[2], "shs": g[5], "scales": g[6], "rotations": g[7]})
+
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    ms = timed_region(step, args.steps, 1, dev)
+    return {"ms_per_step": round(ms / args.steps, 4), "iterations_per_s": round(args.steps / (ms * 1e-3), 2),
+            "what": "rasterizer fwd + fused L1/SSIM loss (value+grad) + rasterizer bwd + fused activation/Adam step, "
+                    "lambda_dssim 0.2, reference learning rates; all b200splat kernels"}
+
+
+def full_iteration_reference(args, w, ref, kw_of, BK, dev):
+    """The same iteration as the reference runs it: its rasterizer kernels, utils/loss_utils.py's torch expression
+    (cuDNN depthwise convs + autograd), torch activations + autograd + torch.optim.Adam(eps=1e-15)."""
+    import torch.nn.functional as F
+    sys.path.insert(0, str(ROOT / "oracle"))
+    import loss_ref                      # the reference's loss expression in torch ops, executed on the GPU here
+    s = w.scene
+    Pm = torch.nn.Parameter
+    xyz, fdc, frest = Pm(s["means3D"].clone()), Pm(s["shs"][:, :1].clone()), Pm(s["shs"][:, 1:].clone())
+    op = Pm(torch.logit(s["opacities"].clamp(1e-6, 1 - 1e-6)))
+    sc, ro = Pm(torch.log(s["scales"])), Pm(s["rotations"].clone())
+    adam = torch.optim.Adam([{"params": [xyz], "lr": 0.00016}, {"params": [fdc], "lr": 0.0025},
+                             {"params": [frest], "lr": 0.0025 / 20.0}, {"params": [op], "lr": 0.05},
+                             {"params": [sc], "lr": 0.005}, {"params": [ro], "lr": 0.001}], lr=0.0, eps=1e-15)
+    gts = [t.to(dev) for t in w.gt_host]
+
+    def step(i):
+        v = w.view_of(i)
+        acts = dict(means3D=xyz, shs=torch.cat((fdc, frest), dim=1), opacities=torch.sigmoid(op), scales=torch.exp(sc),
+                    rotations=F.normalize(ro))
+        kw = kw_of(v)
+        kw.update({k: t.detach() for k, t in acts.items()})
+        R, color, radii = ref.forward(sync=False, **kw)
+        x = color.detach().requires_grad_(True)
+        loss = 0.8 * loss_ref.l1(x, gts[v]) + 0.2 * (1.0 - loss_ref.ssim(x, gts[v]))
+        loss.backward()
+        g = ref.backward(radii=radii, dL_dpix=x.grad, sync=False, **{k: kw[k] for k in BK})
+        torch.autograd.backward([acts["means3D"], acts["shs"], acts["opacities"], acts["scales"], acts["rotations"]],
+                                [g["means3D"], g["sh"].reshape(acts["shs"].shape), g["opacity"].reshape(-1, 1),
+                                 g["scales"], g["rotations"]])
+        adam.step()
+        adam.zero_grad(set_to_none=True)
+
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    ms = timed_region(step, args.steps, 1, dev)
+    return {"ms_per_step": round(ms / args.steps, 4), "iterations_per_s": round(args.steps / (ms * 1e-3), 2),
+            "what": "reference rasterizer kernels + utils/loss_utils.py torch expression + torch autograd through the "
+                    "activations + torch.optim.Adam(eps=1e-15), same learning rates"}
+
+
+def ncu_traffic(stage):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernel, from the newest committed
+    `ncu --set full` summary under profiles/ (captured on the C3 workload by tools/_round.sh); None if absent."""
+    import csv
+    files = sorted((ROOT / "profiles").glob("r*_ncu_full_summary_C3.csv"))
+    if not files:
+        return None, None
+    rows = list(csv.reader(open(files[-1])))
+    hdr, units = rows[0], rows[1]
+    try:
+        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+    except ValueError:
+        return None, None
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for r in rows[2:]:
+        if f"{stage}_kernel" in r[0]:
+            b = float(r[ir]) * scale.get(units[ir], 1.0) + float(r[iw]) * scale.get(units[iw], 1.0)
+            return int(b), f"profiles/{files[-1].name} (ncu --set full, one launch, view 0)"
+    return None, None
 
 
 def roofline_pass(args, w, lib, _C, step_fn):
@@ -372,8 +471,9 @@ def roofline_pass(args, w, lib, _C, step_fn):
     rows = stage_table(w, list(ms), list(calls), args.steps, counts, P_vis, N, hbm_peak, fp32_peak)
     top = max((k for k in rows if "frac" in rows[k]), key=lambda k: rows[k]["ms_per_step"])
     r = rows[top]
+    traffic, traffic_src = ncu_traffic(top)
     roof = {"kernel": top, "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
-            "frac": r["frac"], "traffic": None, "ms_per_launch": r["ms_per_step"],
+            "frac": r["frac"], "traffic": traffic, "traffic_source": traffic_src, "ms_per_launch": r["ms_per_step"],
             "peak_source": (peak_src if r["bound"] == "hbm" else
                             f"nominal FP32 FMA: 148 SM x 128 lanes x 2 x {sm_max:.0f} MHz (no measured FP32 peak)"),
             "share_of_step": round(r["ms_per_step"] / sum(x["ms_per_step"] for x in rows.values()), 4)}
@@ -509,6 +609,7 @@ def run_reference(args, rank, local_rank, world, dev):
         step_e2e(s)
     reduce_finalize()
     ms_e2e = timed_region(step_e2e, args.steps, world, dev, finalize=reduce_finalize)
+    full_it = full_iteration_reference(args, w, ref, kw_of, BK, dev) if world == 1 else None
     ref.close()
     value = round(world * args.steps / (ms_total * 1e-3), 3)
     return {
@@ -533,6 +634,7 @@ def run_reference(args, rank, local_rank, world, dev):
                          "sample": "GPU run of the reference kernels (CUDA-only reference: no host-core path exists); "
                                    f"{args.steps} full steps"},
         "clocks": clk.summary(),
+        **({"full_iteration": full_it} if full_it is not None else {}),
     }
 
 
