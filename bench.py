@@ -203,10 +203,18 @@ def run_ours(args, rank, local_rank, world, dev):
     cfg = w.cfg
     reducer, collective_kind = None, "none"
     if world > 1:
+        peer_ok = torch.ones(1, device=dev)
         if args.collective == "peer":
             # the collective is one kernel of libb200splat.so over NVLink peer memory; the backward writes its
             # gradients straight into the peer-mapped buffers (no staging copy, no NCCL call in the step)
-            reducer = parallel.PeerGradientAllReduce(w.P, 16, dev, ctas=args.peer_ctas, multimem=args.multimem)
+            try:
+                reducer = parallel.PeerGradientAllReduce(w.P, 16, dev, ctas=args.peer_ctas, multimem=args.multimem)
+            except Exception as e:  # noqa: BLE001 — no peer mappings on this box (no NVLink P2P / IPC): say so, use NCCL
+                print(f"[bench] rank {rank}: peer-memory collective unavailable ({e}); falling back to NCCL",
+                      file=sys.stderr)
+                peer_ok.zero_()
+            dist.all_reduce(peer_ok, op=dist.ReduceOp.MIN)
+        if args.collective == "peer" and float(peer_ok.item()) > 0:
             _C.config["grad_out"] = reducer.grad_out
             collective_kind = (f"b200s_peer_allreduce_sum_f32 ({'multimem/NVLS' if reducer.multimem else 'P2P two-shot'}, "
                                f"{reducer.ctas} CTAs, {reducer.mem.backend} mappings"
@@ -214,12 +222,14 @@ def run_ours(args, rank, local_rank, world, dev):
                                   ", dL/dSH rows read only from ranks whose view saw the Gaussian (radii > 0)") + ")")
         else:
             reducer = parallel.GradientAllReduce()
-            collective_kind = "NCCL all_reduce (per-tensor buckets)"
+            _C.config["grad_out"] = None
+            collective_kind = "NCCL all_reduce (per-tensor buckets)" + (
+                "" if args.collective == "nccl" else " — FALLBACK: peer mappings unavailable on this box")
     GRAD_KEYS = {"means3D": 3, "opacities": 2, "shs": 5, "scales": 6, "rotations": 7}   # slots of the 8-tuple
 
     overlap = args.allreduce == "overlap"
 
-    sparse = world > 1 and args.collective == "peer" and args.sparse_collective
+    sparse = args.sparse_collective and isinstance(reducer, parallel.PeerGradientAllReduce)
 
     def reduce_step(grads, radii=None):
         if reducer is None:
