@@ -29,7 +29,11 @@ NUM_FEATURES = 64
 # grad_out: None, or a callable returning {"means3D","opacities","shs","scales","rotations"} -> preallocated float32
 # CUDA tensors the backward writes its gradients into (parallel.PeerGradientAllReduce.grad_out: peer-mapped
 # buffers, so the all-reduce kernel sums them in place with no staging copy).
-config = {"deterministic": False, "optimistic": True, "growth": 1.25, "grad_out": None}
+# early_header: on the optimistic path read the header (num_rendered, preprocess error bits) right after the scan and
+# let the host return while sort + blend are still running, so the caller's loss / backward launches queue up behind
+# them instead of after a full-forward synchronise. Error bits raised by the later stages (look-back watchdogs) are
+# then reported by the NEXT forward call of the thread (no extra synchronisation); debug=True keeps the full check.
+config = {"deterministic": False, "optimistic": True, "growth": 1.25, "grad_out": None, "early_header": True}
 
 _tls = threading.local()
 _capacity_hint = {}   # (device index, P, W, H) -> last num_rendered
@@ -65,6 +69,19 @@ def _pinned_header() -> Tuple[torch.Tensor, "_lib.Header"]:
         buf = torch.zeros(C.sizeof(_lib.Header), dtype=torch.uint8).pin_memory()
         _tls.hdr = buf
     return buf, _lib.Header.from_address(buf.data_ptr())
+
+
+def _pinned_header2() -> Tuple[torch.Tensor, "_lib.Header"]:
+    buf = getattr(_tls, "hdr2", None)
+    if buf is None:
+        buf = torch.zeros(C.sizeof(_lib.Header), dtype=torch.uint8).pin_memory()
+        _tls.hdr2 = buf
+    return buf, _lib.Header.from_address(buf.data_ptr())
+
+
+def _raise_header_error(error: int, where: str = ""):
+    raise RuntimeError(f"b200splat device error flags 0x{error:x}{where}"
+                       + (" (point filtered although prefiltered is set)" if error & 2 else ""))
 
 
 def _read_header(lib, geom: torch.Tensor, device) -> "_lib.Header":
@@ -147,7 +164,29 @@ def _forward_impl(background, means3D, colors, opacity, scales, rotations, scale
         key = (dev.index, P, W, H)
         hint = _capacity_hint.get(key) if config["optimistic"] and not debug else None
         binning = None
-        if hint is not None:
+        if hint is not None and config["early_header"]:
+            binning = alloc_bin(int(hint * config["growth"]) + 4096)
+            # deferred check of the previous forward's late-stage error bits rides on this call's one synchronisation
+            prev = getattr(_tls, "pending_geom", None)
+            buf2, hdr2 = _pinned_header2()
+            if prev is not None and prev.device == dev:
+                _lib.check(lib.b200s_read_header(prev.data_ptr(), buf2.data_ptr(), stream), "b200s_read_header")
+            _lib.check(lib.b200s_forward_preprocess(C.byref(a), stream), "b200s_forward_preprocess")
+            buf, hdr = _pinned_header()
+            _lib.check(lib.b200s_read_header(geom.data_ptr(), buf.data_ptr(), stream), "b200s_read_header")
+            ready = torch.cuda.Event()
+            ready.record(torch.cuda.current_stream(dev))
+            _lib.check(lib.b200s_forward_render(C.byref(a), stream), "b200s_forward_render")
+            ready.synchronize()                        # scan done: sort + blend of this view are still in flight
+            _tls.pending_geom = geom
+            if prev is not None and prev.device == dev and hdr2.error:
+                _tls.pending_geom = None
+                _raise_header_error(hdr2.error, " (raised by the previous forward call)")
+            if hdr.error:
+                _raise_header_error(hdr.error)
+            if int(hdr.num_rendered) > int(a.bin_capacity):      # the device made stage 2 a no-op: redo it exactly
+                binning = None
+        elif hint is not None:
             binning = alloc_bin(int(hint * config["growth"]) + 4096)
             _lib.check(lib.b200s_forward(C.byref(a), stream), "b200s_forward")
             hdr = _read_header(lib, geom, dev)
