@@ -118,7 +118,10 @@ __device__ __forceinline__ T warp_lookback(const T* status, int64_t tile, B200sH
 }
 
 // Per-thread look-back (one chain per radix digit) with LB independent loads in flight per step.
-constexpr int LB_DEPTH = 8;
+#ifndef B200S_LB_DEPTH
+#define B200S_LB_DEPTH 8
+#endif
+constexpr int LB_DEPTH = B200S_LB_DEPTH;
 __device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t stride, int64_t tile, B200sHeader* header) {
     uint32_t excl = 0;
     int64_t t = tile - 1;
@@ -393,19 +396,11 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
     for (int w = 0; w < warp; ++w) wex += s_misc[1 + w];
     const uint32_t dstart = wex + incl - count;
 
-    uint32_t excl = 0;
-    {
-        uint32_t* lb = lookback + (size_t)tile * SORT_RADIX + tid;
-        if (tile == 0) {
-            st_volatile_u32(lb, (count << 2) | FLAG_INCL);
-        } else {
-            st_volatile_u32(lb, (count << 2) | FLAG_AGG);
-            excl = thread_lookback(lookback + tid, SORT_RADIX, (int64_t)tile, header);
-            st_volatile_u32(lb, ((excl + count) << 2) | FLAG_INCL);
-        }
-    }
+    // Publish this tile's digit counts first, scatter locally while the predecessors make progress, and only then
+    // look back: key / val / dr registers are dead by then, so the look-back can keep LB_DEPTH loads in flight.
+    uint32_t* lb = lookback + (size_t)tile * SORT_RADIX + tid;
+    st_volatile_u32(lb, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
     s_dstart[tid] = dstart;
-    s_gbase[tid] = bin_base[tid] + excl - dstart;
     __syncthreads();
 
     // local scatter into digit order
@@ -416,6 +411,12 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         s_keys[pos] = key[k];
         s_vals[pos] = val[k];
     }
+    uint32_t excl = 0;
+    if (tile != 0) {
+        excl = thread_lookback(lookback + tid, SORT_RADIX, (int64_t)tile, header);
+        st_volatile_u32(lb, ((excl + count) << 2) | FLAG_INCL);
+    }
+    s_gbase[tid] = bin_base[tid] + excl - dstart;
     __syncthreads();
     for (uint32_t i = tid; i < tile_n; i += SORT_THREADS) {
         const uint32_t kk = s_keys[i];
