@@ -336,8 +336,11 @@ class DensificationStats:
         self.denom = torch.zeros(P, 1, device=device)
 
     def add_view(self, viewspace_grad: torch.Tensor, visibility: torch.Tensor) -> None:
-        self.accum[visibility] += torch.norm(viewspace_grad[visibility, :2], dim=-1, keepdim=True)
-        self.denom[visibility] += 1
+        # same values as the reference's masked `+=` (gaussian_model.py:551-552) without its boolean-index host sync
+        vis = visibility.reshape(-1, 1)
+        norm = torch.norm(viewspace_grad[:, :2], dim=-1, keepdim=True)
+        self.accum += torch.where(vis, norm, torch.zeros_like(norm))
+        self.denom += vis.to(self.denom.dtype)
 
     def allreduce(self, group=None) -> None:
         if dist.is_initialized() and dist.get_world_size(group) > 1:
