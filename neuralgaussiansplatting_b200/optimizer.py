@@ -126,6 +126,28 @@ class FusedGaussianAdam:
                        "b200s_adam_step")
         del keep
 
+    # ---- adaptive density control (densify.py): hand the tensors out as a GaussianState, take a resized one back
+    def densify_state(self, grad_accum: torch.Tensor, denom: torch.Tensor, max_radii2D: Optional[torch.Tensor] = None,
+                      extras: Optional[Dict[str, torch.Tensor]] = None):
+        from .densify import GaussianState
+        P = self.raw["xyz"].shape[0]
+        if max_radii2D is None:
+            max_radii2D = torch.zeros(P, device=self.raw["xyz"].device)
+        return GaussianState(dict(self.raw), dict(self.exp_avg), dict(self.exp_avg_sq), grad_accum, denom, max_radii2D,
+                             dict(extras or {}))
+
+    def load_densified(self, state) -> None:
+        """Install the tensors of a GaussianState whose P may differ (clone / split / prune, reset_opacity): raw
+        parameters and moments are replaced, the activated tensors recomputed. step_count is kept: the reference keeps
+        each survivor's Adam `step` and new rows join with zero moments (cat_tensors_to_optimizer)."""
+        for name in self.raw:
+            self.raw[name] = state.params[name].contiguous()
+            self.exp_avg[name] = state.exp_avg[name].contiguous()
+            self.exp_avg_sq[name] = state.exp_avg_sq[name].contiguous()
+        for act_name, (raw_name, mode) in TENSORS.items():
+            self.activated[act_name] = (self.raw[raw_name] if mode in ("identity", "sh")
+                                        else activate(act_name, self.raw[raw_name]).contiguous())
+
     # ---- interchange with the reference's layout (checkpoints: gaussian_model.py capture()/restore())
     def reference_tensors(self) -> Dict[str, torch.Tensor]:
         """{_xyz, _features_dc[P,1,3], _features_rest[P,15,3], _opacity, _scaling, _rotation} copies."""

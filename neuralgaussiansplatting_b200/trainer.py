@@ -103,6 +103,34 @@ class ViewParallelTrainer:
         self.opt.step(total)
         return loss3
 
+    # ------------------------------------------------------------------ adaptive density control
+    def _make_reducer(self):
+        if self.world > 1 and self.collective == "peer":
+            self.reducer = None                                   # release the old peer buffers first
+            torch.cuda.empty_cache()
+            self.reducer = parallel.PeerGradientAllReduce(self.P, 16, self.dev, group=self.group)
+
+    def densify_and_prune(self, max_grad: float = 0.0002, min_opacity: float = 0.005, extent: float = 1.0,
+                          max_screen_size: Optional[float] = None, percent_dense: float = 0.01) -> int:
+        """train.py:113-121 for a view-parallel job: the per-view statistics are summed over ranks first, the split's
+        noise comes from a generator seeded with the iteration number, so every replica takes the same decisions and
+        ends with bit-identical tensors. Returns the new number of Gaussians."""
+        from .densify import densify_and_prune
+        self.stats.allreduce(self.group)
+        gen = torch.Generator(device=self.dev).manual_seed(1_000_003 * self.iteration + 17)
+        st = self.opt.densify_state(self.stats.accum, self.stats.denom)
+        st = densify_and_prune(st, max_grad, min_opacity, extent, max_screen_size, percent_dense, generator=gen)
+        self.opt.load_densified(st)
+        self.P = st.P
+        self.stats = parallel.DensificationStats(self.P, self.dev)
+        self._make_reducer()
+        return self.P
+
+    def reset_opacity(self) -> None:
+        from .densify import reset_opacity
+        st = reset_opacity(self.opt.densify_state(self.stats.accum, self.stats.denom))
+        self.opt.load_densified(st)
+
     # ------------------------------------------------------------------ checks / export
     def replicas_in_sync(self) -> bool:
         return parallel.replicas_in_sync(self.opt.raw.values(), self.group)

@@ -31,3 +31,8 @@ def test_two_rank_training_keeps_replicas_bit_identical():
         pytest.skip("needs 2 GPUs")
     rep = _run(2, "--cfg", "T1", "--iters", "40")
     assert rep["replicas_in_sync"] and rep["collective"] in ("peer", "nccl"), rep
+
+
+def test_densification_inside_the_training_loop_changes_P_and_training_continues():
+    rep = _run(1, "--cfg", "T1", "--iters", "40", "--densify-at", "20")
+    assert rep["densified"][0] == 20000 and rep["densified"][1] != 20000 and rep["P"] == rep["densified"][1], rep

@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--cfg", default="T1")
     ap.add_argument("--iters", type=int, default=60)
     ap.add_argument("--views", type=int, default=8)
+    ap.add_argument("--densify-at", type=int, default=0, help="iteration after which to run densify_and_prune once")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank, local = int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
@@ -43,18 +44,25 @@ def main():
     target = ViewParallelTrainer(raw_from_scene(sc, dev), collective="none")
     gts = [target.render(c).clone() for c in cams]
     tr = ViewParallelTrainer(raw_from_scene(sc, dev, noise=1.0, seed=7))          # same perturbation on every rank
-    losses = []
+    losses, densified = [], None
     for it in range(a.iters):
         v = (it * world + rank) % a.views
         losses.append(tr.step(cams[v], gts[v]))
+        if a.densify_at and it + 1 == a.densify_at:
+            p0 = tr.P
+            p1 = tr.densify_and_prune(max_grad=2e-6, min_opacity=0.005, extent=4.0)
+            densified = (p0, p1)
     torch.cuda.synchronize()
     vals = [float(x[0]) for x in losses]
     rep = {"world": world, "collective": tr.collective, "P": tr.P, "iters": a.iters,
            "loss_first5": round(sum(vals[:5]) / 5, 5), "loss_last5": round(sum(vals[-5:]) / 5, 5),
-           "replicas_in_sync": tr.replicas_in_sync()}
+           "replicas_in_sync": tr.replicas_in_sync(), "densified": densified}
     if rank == 0:
         print(json.dumps(rep))
-    assert rep["loss_last5"] < rep["loss_first5"], rep
+    if densified is None:       # a densification step re-opens the loss (clones double their parents' density at first)
+        assert rep["loss_last5"] < rep["loss_first5"], rep
+    else:
+        assert densified[1] != densified[0], rep
     assert rep["replicas_in_sync"], rep
     if world > 1:
         dist.destroy_process_group()
