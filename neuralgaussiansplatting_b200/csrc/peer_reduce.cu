@@ -49,6 +49,7 @@ struct PeerReduceParams {
     size_t vis_off;        // byte offset of the visibility array from bufs[r]
 };
 
+constexpr unsigned long long PR_BARRIER_TIMEOUT_NS = 60ull * 1000000000ull;   // peers start within a minute or never
 constexpr int PR_CHUNK = 1024;   // rows per work unit of the sparse tail
 constexpr int PR_ROW4 = 12;      // float4 per row: 16 SH coefficients x 3 channels
 
@@ -102,7 +103,20 @@ __device__ __forceinline__ void peer_barrier(const PeerReduceParams& p, int phas
         __threadfence_system();
         st_release_sys(p.flags[peer] + flag_slot(phase, blockIdx.x, gridDim.x, p.rank, p.world), p.epoch);
         const uint32_t* mine = p.flags[p.rank] + flag_slot(phase, blockIdx.x, gridDim.x, peer, p.world);
-        while ((int32_t)(ld_acquire_sys(mine) - p.epoch) < 0) __nanosleep(64);
+        // Failure detection: a peer that died (or never launched this collective) must not hang this GPU for good.
+        // After PR_BARRIER_TIMEOUT_NS without the peer's flag the kernel traps, which surfaces as a CUDA error on the
+        // host's next synchronisation instead of a silent hang.
+        uint32_t spins = 0;
+        unsigned long long t0 = 0;
+        while ((int32_t)(ld_acquire_sys(mine) - p.epoch) < 0) {
+            __nanosleep(64);
+            if ((++spins & 0x3fffu) == 0u) {
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > PR_BARRIER_TIMEOUT_NS) __trap();
+            }
+        }
     }
     __syncthreads();
 }
