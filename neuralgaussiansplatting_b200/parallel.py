@@ -127,6 +127,31 @@ def gradient_layout(P: int, sh_coeffs: int = 16, align_floats: int = 64):
     return out, off
 
 
+def peer_owner_slices(n_float4: int, world: int):
+    """[(begin, end)] of the float4 elements each rank reduces in b200s_peer_allreduce_sum_f32 (csrc/peer_reduce.cu:
+    per = ceil(n4 / world); rank r owns [min(n4, r*per), min(n4, r*per + per)))."""
+    per = -(-n_float4 // world)
+    return [(min(n_float4, r * per), min(n_float4, r * per + per)) for r in range(world)]
+
+
+def peer_sparse_chunks(rows: int, world: int, ctas: int, chunk: int = 1024):
+    """{(rank, cta): [(row_begin, row_end), ...]} — the 1024-row work units of the visibility-sparse tail: rank r owns
+    rows [r*rows_per, (r+1)*rows_per) with rows_per = ceil(ceil(rows/world)/1024)*1024; its CTA b takes chunks
+    b, b+ctas, ... and stops at the first chunk starting at or beyond `rows`."""
+    rows_per = -(-(-(-rows // world)) // chunk) * chunk
+    out = {}
+    for r in range(world):
+        for b in range(ctas):
+            lst = []
+            for c in range(b, rows_per // chunk, ctas):
+                row0 = r * rows_per + c * chunk
+                if row0 >= rows:
+                    break
+                lst.append((row0, min(rows, row0 + chunk)))
+            out[(r, b)] = lst
+    return out
+
+
 class PeerMemory:
     """`nbytes` of device memory on every rank of the group, each rank's block mapped into every other rank's
     address space over NVLink (plumbing only: the kernels that use the mappings are in libb200splat.so).

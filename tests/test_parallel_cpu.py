@@ -58,6 +58,26 @@ def test_gradient_layout_is_aligned_and_disjoint():
     assert total * 4 == par.allreduce_payload_bytes(3_000_000)     # no padding at the bench size
 
 
+def test_peer_collective_partitions_cover_every_element_exactly_once():
+    from neuralgaussiansplatting_b200 import _lib
+    lib = _lib.load()
+    for world in (2, 3, 4, 8):
+        for n4 in (0, 1, 7, 8, 1000, 44_250_000):
+            sl = par.peer_owner_slices(n4, world)
+            assert sl[0][0] == 0 and sl[-1][1] == n4
+            assert all(a[1] == b[0] for a, b in zip(sl, sl[1:])) and all(b >= a for a, b in sl)
+        for rows in (1, 1023, 1024, 1025, 10_007, 3_000_000):
+            rows_per = lib.b200s_peer_allreduce_rows_per_rank(rows, world)
+            assert rows_per % 1024 == 0 and rows_per * world >= rows and rows_per == -(-(-(-rows // world)) // 1024) * 1024
+            assert lib.b200s_peer_allreduce_vis_bytes(rows, world) == rows_per * world
+            for ctas in (1, 8, 16):
+                spans = sorted(sp for lst in par.peer_sparse_chunks(rows, world, ctas).values() for sp in lst)
+                assert spans[0][0] == 0 and spans[-1][1] == rows
+                assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))          # no gap, no overlap
+    lay, total = par.gradient_layout(3_000_000)
+    assert lay["shs"][0] % 4 == 0 and lay["shs"][0] + 3_000_000 * 48 == total      # sparse tail = last tensor
+
+
 def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
 
