@@ -124,3 +124,20 @@ def test_check_turns_status_into_runtime_error():
         _lib.check(-2, "x")
     with pytest.raises(RuntimeError, match="CUDA error 700"):
         _lib.check(700, "x")
+
+
+def test_header_is_plain_c99(tmp_path):
+    """The drop-in boundary must be bindable from C (cgo / JNI / ctypes / a torch extension): no C++ in the header."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    src = tmp_path / "h.c"
+    src.write_text('#include "b200splat.h"\n'
+                   'int main(void) { B200sForwardArgs f; B200sBackwardArgs b; B200sIdxmapArgs i; B200sPeerReduceArgs p;\n'
+                   '  B200sAdamArgs a; B200sLossArgs l; (void)f; (void)b; (void)i; (void)p; (void)a; (void)l;\n'
+                   '  return (int)sizeof(B200sHeader) - 64; }\n')
+    inc = Path(__file__).resolve().parent.parent / "include"
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", str(inc), "-c", str(src), "-o",
+                        str(tmp_path / "h.o")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
