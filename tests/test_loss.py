@@ -37,6 +37,34 @@ def test_oracle_identities():
     assert w.shape == (3, 1, 11, 11) and abs(float(w[0].sum()) - 1.0) < 1e-6 and torch.equal(w[0], w[2])
 
 
+GOLDEN = ROOT / "tests" / "golden" / "ref_loss.npz"      # produced by the reference's own utils/loss_utils.py
+
+
+def test_oracle_reproduces_the_reference_golden():
+    import numpy as np
+    z = np.load(GOLDEN)
+    for name in ("a", "b", "c"):
+        img, gt, lam = torch.tensor(z[f"{name}_img"]), torch.tensor(z[f"{name}_gt"]), float(z[f"{name}_lambda"])
+        loss, l1, ssim, grad = loss_ref.loss_and_grad(img, gt, lam, torch.float32)
+        assert abs(float(l1) - float(z[f"{name}_l1"])) < 1e-7 and abs(float(ssim) - float(z[f"{name}_ssim"])) < 1e-6
+        assert abs(float(loss) - float(z[f"{name}_loss"])) < 1e-6
+        ref_g = torch.tensor(z[f"{name}_grad"])
+        assert float((grad - ref_g).norm() / ref_g.norm()) < 1e-5, name
+
+
+@pytest.mark.gpu
+def test_fused_loss_matches_the_reference_golden():
+    import numpy as np
+    z = np.load(GOLDEN)
+    dev = torch.device("cuda:0")
+    for name in ("a", "b", "c"):
+        img, gt, lam = torch.tensor(z[f"{name}_img"]), torch.tensor(z[f"{name}_gt"]), float(z[f"{name}_lambda"])
+        out, grad = L.fused_l1_ssim(img.to(dev), gt.to(dev), lam)
+        assert abs(float(out[0]) - float(z[f"{name}_loss"])) < 5e-6 and abs(float(out[2]) - float(z[f"{name}_ssim"])) < 5e-6
+        ref_g = torch.tensor(z[f"{name}_grad"])
+        assert float((grad.cpu() - ref_g).norm() / ref_g.norm()) < 1e-4, name
+
+
 def test_oracle_gradient_matches_finite_differences():
     img, gt = _pair(1, 12, 14, 1)
     _, _, _, g = loss_ref.loss_and_grad(img, gt, 0.2, torch.float64)
