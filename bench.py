@@ -115,6 +115,18 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
 
 
+def load_sm_peaks(sm_max_mhz):
+    """FP32-FMA / MUFU / shared-memory / issue-slot peaks of this pool's B200 measured by tools/sm_peaks (a
+    register-resident micro-benchmark timed with CUDA events); the newest profiles/r*_sm_peaks.json. Falls back to
+    the nominal figures (and says so) when no measurement is committed."""
+    files = sorted((ROOT / "profiles").glob("r*_sm_peaks.json"))
+    if files:
+        d = json.loads(files[-1].read_text())
+        return d, f"measured by tools/sm_peaks on this pool's B200 (profiles/{files[-1].name})"
+    nominal = {"fp32_tflops": 148 * 128 * 2 * sm_max_mhz * 1e6 / 1e12, "issue_ginst_per_s": 148 * 4 * sm_max_mhz * 1e6 / 1e9}
+    return nominal, f"nominal: 148 SM x 128 lanes x 2 x {sm_max_mhz:.0f} MHz (no measured SM peaks committed)"
+
+
 # ----------------------------------------------------------------------------------------- workload
 class Workload:
     """C3: 3 M replicated Gaussians, 8 orbit views, per-view dL/dimage and ground-truth images."""
@@ -172,6 +184,16 @@ def stage_table(w: Workload, stage_ms, stage_calls, steps, counts, P_vis, N, hbm
         "blend_bwd": ("fp32", 14 * n_trav_bwd + 69 * n_contrib),
         "preprocess_bwd": ("hbm", 510 * P_vis + 4 * P_c + 236 * P_c),
     }
+    # Bytes THIS implementation moves per launch, where they differ from the algorithmic figure above
+    # (which, for the binning stages, is the reference's 64-bit CUB sort of all instances): the in-house sort moves
+    # u32 tile keys + u32 ids through `tile_passes` onesweep passes and presorts the visible set on depth.
+    tile_passes = -(-max(T - 1, 1).bit_length() // 8)
+    moved = {
+        "scan": 4 * P + 8 * P_vis,
+        "expand": 4 * 16 * P_vis + 8 * N,
+        "sort": 16 * N * tile_passes + 4 * N,
+        "ranges": 4 * N + 8 * T,
+    }
     rows = {}
     for i, name in enumerate(_lib.STAGES):
         if stage_calls[i] == 0:
@@ -184,6 +206,11 @@ def stage_table(w: Workload, stage_ms, stage_calls, steps, counts, P_vis, N, hbm
                 ach = units / (ms * 1e-3) / 1e9
                 row.update(bound="hbm", algorithmic_bytes=int(units), achieved=round(ach, 1), peak=hbm_peak,
                            unit="GB/s", frac=round(ach / hbm_peak, 4))
+                if name in moved:
+                    row.update(moved_bytes=int(moved[name]),
+                               moved_gbps=round(moved[name] / (ms * 1e-3) / 1e9, 1),
+                               note="frac is quoted on the reference's algorithmic bytes; moved_bytes is what these "
+                                    "kernels actually move (latency / ADU-pipe bound, not HBM)")
             else:
                 ach = units / (ms * 1e-3) / 1e12
                 row.update(bound="fp32", algorithmic_flops=int(units), achieved=round(ach, 3),
@@ -199,6 +226,7 @@ def run_ours(args, rank, local_rank, world, dev):
     from neuralgaussiansplatting_b200.diff_gaussian_rasterization import (GaussianRasterizationSettings,
                                                                           GaussianRasterizer)
     lib = _lib.load()          # raises if libb200splat.so is missing: there is no fallback path
+    _C.config["blend_mode"] = 1 if args.blend_mode == "fast" else 0
     w = Workload(args.workload, dev, rank, world)
     cfg = w.cfg
     reducer, collective_kind = None, "none"
@@ -208,33 +236,39 @@ def run_ours(args, rank, local_rank, world, dev):
             # the collective is one kernel of libb200splat.so over NVLink peer memory; the backward writes its
             # gradients straight into the peer-mapped buffers (no staging copy, no NCCL call in the step)
             try:
-                reducer = parallel.PeerGradientAllReduce(w.P, 16, dev, ctas=args.peer_ctas, multimem=args.multimem)
+                reducer = parallel.PeerGradientAllReduce(w.P, 16, dev, ctas=args.peer_ctas, multimem=args.multimem,
+                                                         factored=not args.dense_collective)
             except Exception as e:  # noqa: BLE001 — no peer mappings on this box (no NVLink P2P / IPC): say so, use NCCL
                 print(f"[bench] rank {rank}: peer-memory collective unavailable ({e}); falling back to NCCL",
                       file=sys.stderr)
                 peer_ok.zero_()
             dist.all_reduce(peer_ok, op=dist.ReduceOp.MIN)
         if args.collective == "peer" and float(peer_ok.item()) > 0:
-            _C.config["grad_out"] = reducer.grad_out
             collective_kind = (f"b200s_peer_allreduce_sum_f32 ({'multimem/NVLS' if reducer.multimem else 'P2P two-shot'}, "
                                f"{reducer.ctas} CTAs, {reducer.mem.backend} mappings"
-                               + ("" if not args.sparse_collective or reducer.multimem else
+                               + (", factored SH gradient: 11 dense floats summed + 3 dL/dRGB floats gathered per Gaussian "
+                                  "and view, dL/dsh rebuilt by b200s_sh_grad_reconstruct (bit-identical to the dense sum)"
+                                  if reducer.factored else "")
+                               + ("" if not args.sparse_collective or reducer.multimem or reducer.factored else
                                   ", dL/dSH rows read only from ranks whose view saw the Gaussian (radii > 0)") + ")")
         else:
-            reducer = parallel.GradientAllReduce()
-            _C.config["grad_out"] = None
-            collective_kind = "NCCL all_reduce (per-tensor buckets)" + (
+            reducer = parallel.FlatGradientAllReduce(w.P, 16, dev)
+            collective_kind = "NCCL all_reduce, one call on a flat buffer the backward writes into" + (
                 "" if args.collective == "nccl" else " — FALLBACK: peer mappings unavailable on this box")
+        _C.config["grad_out"] = reducer.grad_out
     GRAD_KEYS = {"means3D": 3, "opacities": 2, "shs": 5, "scales": 6, "rotations": 7}   # slots of the 8-tuple
 
     overlap = args.allreduce == "overlap"
 
-    sparse = args.sparse_collective and isinstance(reducer, parallel.PeerGradientAllReduce)
+    is_peer = isinstance(reducer, parallel.PeerGradientAllReduce)
+    sparse = args.sparse_collective and is_peer and not reducer.factored
 
-    def reduce_step(grads, radii=None):
+    def reduce_step(grads, radii=None, means3D=None):
         if reducer is None:
             return
         kw = {"radii": radii} if (sparse and radii is not None) else {}
+        if is_peer:
+            kw.update(means3D=w.scene["means3D"] if means3D is None else means3D, sh_degree=3)
         if overlap:
             reducer.wait()          # the reduce of the PREVIOUS view ran while this view was rasterized
             reducer.start(grads, **kw)
@@ -291,7 +325,7 @@ def run_ours(args, rank, local_rank, world, dev):
                                                   cov3D_precomp=None)
         loss = (img - gt_dev).abs().mean()
         loss.backward()
-        reduce_step({k: p.grad for k, p in params.items()}, radii=radii)
+        reduce_step({k: p.grad for k, p in params.items()}, radii=radii, means3D=params["means3D"].detach())
         if losses.push(loss) is not None:                 # loss of the previous step is now on the host
             state["read"] += 1
         for p in params.values():
@@ -334,7 +368,8 @@ def run_ours(args, rank, local_rank, world, dev):
                    "collective": collective_kind,
                    "parallelism": f"view-parallel x{world}, Gaussians replicated",
                    "l2": "inputs (708 MB of Gaussian parameters) exceed the 126 MB L2; no explicit flush",
-                   "blend_mode": "strict (expf, bit-exact n_contrib)"},
+                   "blend_mode": BLEND_MODES[_C.config.get("blend_mode", 0)],
+                   "what": "this repo's sm_100a kernels (libb200splat.so) through the drop-in _C binding"},
         "e2e": {"value": round(world * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
                 "ms_per_step": round(ms_e2e / args.steps, 4), "h2d_bytes_per_step": w.h2d_bytes,
                 "d2h_bytes_per_step": w.d2h_bytes,
@@ -343,13 +378,76 @@ def run_ours(args, rank, local_rank, world, dev):
         "gpu_launches": launches,
         "clocks": clk.summary(),
     }
+    if world > 1:
+        out["collective_check"] = collective_check(w, reducer, _C, step_resident, GRAD_KEYS, rank, world, dev)
+    _C.config["grad_out"] = None
     if world == 1:
         out["full_iteration"] = full_iteration_ours(args, w, _C, dev)
     if rank == 0:
         out.update(roofline_pass(args, w, lib, _C, lambda s: step_resident(s, collective=False)))
         if not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(w)
+    if not args.no_render_only:
+        del w
+        torch.cuda.empty_cache()
+        ro = render_only(args, rank, world, dev, "ours")
+        if rank == 0:
+            out["render_only"] = ro
     return out
+
+
+BLEND_MODES = {0: "strict (expf, bit-exact n_contrib)", 1: "fast (ex2.approx falloff, forward and backward)"}
+
+
+def collective_check(w, reducer, _C, step_resident, GRAD_KEYS, rank, world, dev):
+    """Correctness of the gradient collective inside the driver-run path (N > 1), after the timed region: one more
+    step in deterministic-backward mode (bit-reproducible local gradients) through the collective under test, then
+    the same local gradients (a) all-gathered and summed in rank order with torch — must be BIT-identical to what the
+    collective delivered — and (b) through one dist.all_reduce (NCCL's own order: equal to rounding)."""
+    saved = (_C.config["grad_out"], _C.config["deterministic"])
+    s_check = 10_000
+    try:
+        _C.config["deterministic"] = True
+        g = step_resident(s_check, collective=True)
+        reducer.wait()
+        torch.cuda.synchronize(dev)
+        got = {k: g[i].clone() for k, i in GRAD_KEYS.items()}
+        _C.config["grad_out"] = None
+        g2 = step_resident(s_check, collective=False)
+        local = {k: g2[i] for k, i in GRAD_KEYS.items()}
+        res = {"max_abs_diff_vs_nccl": 0.0, "max_rel_diff_vs_nccl": 0.0, "bit_identical_to_fixed_order_sum": True,
+               "replicas_identical": True}
+        for k, t in local.items():
+            parts = [torch.empty_like(t) for _ in range(world)]
+            dist.all_gather(parts, t.contiguous())
+            fixed = parts[0].clone()
+            for q in parts[1:]:
+                fixed += q
+            del parts
+            if not torch.equal(fixed, got[k].reshape(fixed.shape)):
+                res["bit_identical_to_fixed_order_sum"] = False
+                res.setdefault("mismatch", {})[k] = float((fixed - got[k].reshape(fixed.shape)).abs().max())
+            nc = t.clone()
+            dist.all_reduce(nc, op=dist.ReduceOp.SUM)
+            d = (nc - got[k].reshape(nc.shape)).abs().max()
+            res["max_abs_diff_vs_nccl"] = max(res["max_abs_diff_vs_nccl"], float(d))
+            res["max_rel_diff_vs_nccl"] = max(res["max_rel_diff_vs_nccl"], float(d / nc.abs().max().clamp_min(1e-30)))
+            chk = got[k].double().sum().reshape(1)
+            allc = [torch.empty_like(chk) for _ in range(world)]
+            dist.all_gather(allc, chk)
+            if not all(torch.equal(allc[0], c) for c in allc[1:]):
+                res["replicas_identical"] = False
+            del fixed, nc
+        flag = torch.tensor([1.0 if res["bit_identical_to_fixed_order_sum"] and res["replicas_identical"] else 0.0],
+                            device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        res["all_ranks_ok"] = bool(flag.item() > 0)
+        res["what"] = ("one extra step, deterministic backward; collective result vs rank-order torch sum of an "
+                       "all_gather (bit-exact) and vs dist.all_reduce (NCCL order)")
+        return res
+    finally:
+        _C.config["grad_out"], _C.config["deterministic"] = saved
+
 
 
 def full_iteration_ours(args, w, _C, dev):
@@ -551,10 +649,20 @@ def run_reference(args, rank, local_rank, world, dev):
         return {"impl": "reference", "unavailable": "oracle/_ref/libref_dgr.so was not built (needs /root/reference)"}
     w = Workload(args.workload, dev, rank, world)
     cfg = w.cfg
+    h2d_bytes, d2h_bytes = w.h2d_bytes, w.d2h_bytes
     ref = refbind.RefDGR()
-    reducer = parallel.GradientAllReduce() if world > 1 else None
+    # N > 1: the strongest plain-NCCL formulation — ONE ncclAllReduce on a flat buffer the reference's backward
+    # accumulates into (the binding's nine torch::zeros become zero-fills of views of that buffer: same memset bytes)
+    reducer = parallel.FlatGradientAllReduce(w.P, 16, dev) if world > 1 else None
     overlap = args.allreduce == "overlap"      # same communication mode as our arm: the all-reduce is ours in both
     s_ = w.scene
+
+    def grad_views():
+        if reducer is None:
+            return None
+        v = reducer.grad_out()
+        return {"means3D": v["means3D"], "opacity": v["opacities"], "sh": v["shs"], "scales": v["scales"],
+                "rotations": v["rotations"]}
 
     def reduce_step(g):
         if reducer is None:
@@ -584,7 +692,7 @@ def run_reference(args, rank, local_rank, world, dev):
 
     def fwd_bwd(kw, dL):
         R, color, radii = ref.forward(sync=False, **kw)
-        g = ref.backward(radii=radii, dL_dpix=dL, sync=False, **{k: kw[k] for k in BK})
+        g = ref.backward(radii=radii, dL_dpix=dL, sync=False, out=grad_views(), **{k: kw[k] for k in BK})
         reduce_step(g)
         return color
 
@@ -592,60 +700,184 @@ def run_reference(args, rank, local_rank, world, dev):
         v = w.view_of(s)
         fwd_bwd(kw_of(v), w.dL[v])
 
-    cam_dev = torch.empty(35, device=dev)
-    gt_dev = torch.empty(3, cfg.height, cfg.width, device=dev)
-    loss_host = torch.zeros(1).pin_memory()
+    # e2e: the SAME host loop as our arm (pipeline.ViewPrefetcher uploads view k+1 behind view k, the loss is read one
+    # step late through DeferredScalar), so the e2e ratio compares rasterizers, not host pipelining.
+    from neuralgaussiansplatting_b200.pipeline import DeferredScalar, ViewPrefetcher
+    pf = ViewPrefetcher(dev, {"cam": ((35,), torch.float32), "gt": ((3, cfg.height, cfg.width), torch.float32)})
+    losses = DeferredScalar(lag=1)
+    state = {"steps": 0, "submitted": 0, "read": 0}
+
+    def host_view(s):
+        v = w.view_of(s)
+        return {"cam": w.cam_host[v], "gt": w.gt_host[v]}
 
     def step_e2e(s):
         v = w.view_of(s)
-        cam_dev.copy_(w.cam_host[v], non_blocking=True)
-        gt_dev.copy_(w.gt_host[v], non_blocking=True)
+        if state["submitted"] == 0:
+            pf.submit(host_view(s)); state["submitted"] += 1
+        buf = pf.acquire()
+        if state["submitted"] < state["steps"]:
+            pf.submit(host_view(s + 1)); state["submitted"] += 1
+        cam_dev, gt_dev = buf["cam"], buf["gt"]
         kw = kw_of(v, cam_dev[0:16].view(4, 4), cam_dev[16:32].view(4, 4), cam_dev[32:35])
         R, color, radii = ref.forward(sync=False, **kw)
         diff = color - gt_dev
         loss = diff.abs().mean()
         dL = torch.sign(diff) / diff.numel()                 # d(L1 mean)/d(color), what autograd would hand back
-        g = ref.backward(radii=radii, dL_dpix=dL, sync=False, **{k: kw[k] for k in BK})
+        g = ref.backward(radii=radii, dL_dpix=dL, sync=False, out=grad_views(), **{k: kw[k] for k in BK})
         reduce_step(g)
-        loss_host.copy_(loss.reshape(1), non_blocking=True)
+        if losses.push(loss) is not None:
+            state["read"] += 1
+
+    def e2e_begin(steps):
+        state.update(steps=steps, submitted=0, read=0)
+
+    def e2e_finalize():
+        reduce_finalize()
+        pf.release()
+        state["read"] += len(losses.drain())
         torch.cuda.current_stream().synchronize()
+        assert state["read"] == state["steps"] and state["submitted"] == state["steps"], state
 
     for s in range(args.warmup):
         step_resident(s)
     reduce_finalize()
     with ClockSampler(local_rank) as clk:
         ms_total = timed_region(step_resident, args.steps, world, dev, finalize=reduce_finalize)
-    for s in range(max(args.warmup, 3)):
+    nw = max(args.warmup, 3)
+    e2e_begin(nw)
+    for s in range(nw):
         step_e2e(s)
-    reduce_finalize()
-    ms_e2e = timed_region(step_e2e, args.steps, world, dev, finalize=reduce_finalize)
+    e2e_finalize()
+    e2e_begin(args.steps)
+    ms_e2e = timed_region(step_e2e, args.steps, world, dev, finalize=e2e_finalize)
     full_it = full_iteration_reference(args, w, ref, kw_of, BK, dev) if world == 1 else None
     ref.close()
     value = round(world * args.steps / (ms_total * 1e-3), 3)
+    workload_name = (f"{cfg.name}: {w.P} Gaussians SH3, {cfg.width}x{cfg.height}, fwd+bwd, 1 view/step/GPU "
+                     f"cycling {w.nviews} orbit views" + (", + SUM all-reduce of 59 floats/Gaussian" if world > 1 else ""))
+    ro = None
+    if not args.no_render_only:
+        del w
+        torch.cuda.empty_cache()
+        ro = render_only(args, rank, world, dev, "reference")
     return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms_total / args.steps, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{cfg.name}: {w.P} Gaussians SH3, {cfg.width}x{cfg.height}, fwd+bwd, 1 view/step/GPU "
-                               f"cycling {w.nviews} orbit views" + (", + NCCL SUM all-reduce of 59 floats/Gaussian"
-                                                                     if world > 1 else ""),
+        "config": {"workload": workload_name,
                    "allreduce": ("none (1 GPU)" if world == 1 else
-                                 "overlap: the reduce of view k runs on the NCCL stream while view k+1 is rasterized "
+                                 "overlap: the reduce of view k runs on a side stream while view k+1 is rasterized "
                                  "(north_star); every reduce completes inside the timed region" if overlap else
                                  "blocking: reduce exposed after every view"),
+                   "collective": ("none" if world == 1 else
+                                  "NCCL all_reduce, one call on a flat buffer the backward accumulates into"),
                    "parallelism": f"view-parallel x{world}, Gaussians replicated",
+                   "l2": "inputs (708 MB of Gaussian parameters) exceed the 126 MB L2; no explicit flush",
+                   "blend_mode": "strict (expf; the reference has no other mode)",
                    "what": "unmodified reference diff-gaussian-rasterization kernels compiled for sm_100 "
                            "(oracle/_ref), same GPU, same inputs; the reference has no CPU implementation of this "
                            "path and no multi-GPU code (the all-reduce at N>1 is this repo's NCCL plumbing)"},
         "e2e": {"value": round(world * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
-                "ms_per_step": round(ms_e2e / args.steps, 4), "h2d_bytes_per_step": w.h2d_bytes,
-                "d2h_bytes_per_step": w.d2h_bytes},
+                "ms_per_step": round(ms_e2e / args.steps, 4), "h2d_bytes_per_step": h2d_bytes,
+                "d2h_bytes_per_step": d2h_bytes,
+                "api": "reference kernels behind the same host loop as our arm: pipeline.ViewPrefetcher (next view "
+                       "uploads behind the current one), loss read one step late"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
                          "sample": "GPU run of the reference kernels (CUDA-only reference: no host-core path exists); "
                                    f"{args.steps} full steps"},
         "clocks": clk.summary(),
         **({"full_iteration": full_it} if full_it is not None else {}),
+        **({"render_only": ro} if ro is not None else {}),
     }
+
+
+# ----------------------------------------------------------------------------------------- render-only (C4)
+def render_only(args, rank, world, dev, impl):
+    """The other half of BASELINE.json's metric: render-only views/s, config C4 (6 M Gaussians, SH3, 1920x1080, 64
+    orbit views), view-parallel — Gaussians replicated, view v on rank v mod N, no communication (the analogue of
+    render.py:24-35's `for view in views: render(view, ...)["render"]` under no_grad). `value` = all 64 views x
+    passes / max-over-ranks device time with everything resident; `e2e` adds, per view, the camera block H2D (pinned)
+    and the rendered image D2H into pinned host memory (double-buffered, as render.py hands every image to the
+    host for torchvision.save_image, :32) inside the timed region. The reference arm loops the unmodified reference
+    forward (oracle/_ref) exactly the same way."""
+    from neuralgaussiansplatting_b200 import parallel
+    from neuralgaussiansplatting_b200.synthetic import CONFIGS, make_camera, make_scene
+    cfg = CONFIGS["C4"]
+    nviews, passes = 64, max(1, args.render_passes)
+    sc = {k: v.to(dev) for k, v in make_scene(cfg, seed=0).items() if k not in ("feature_vector", "normal")}
+    mine = parallel.shard_views(nviews, rank, world)
+    cams_h = {v: make_camera(cfg, v) for v in mine}
+    cams = {v: make_camera(cfg, v, device=dev) for v in mine}
+    cam_host = {v: torch.cat([c.world_view_transform.reshape(-1), c.full_proj_transform.reshape(-1),
+                              c.camera_center.reshape(-1)]).pin_memory() for v, c in cams_h.items()}
+    bg = torch.zeros(3, device=dev)
+    tan = (math.tan(cfg.fovx * 0.5), math.tan(cfg.fovy * 0.5))
+    E = torch.Tensor([])
+    if impl == "ours":
+        from neuralgaussiansplatting_b200 import _C
+
+        def render(view, proj, campos):
+            return _C.rasterize_gaussians(bg, sc["means3D"], E, sc["opacities"], sc["scales"], sc["rotations"], 1.0, E,
+                                          view, proj, tan[0], tan[1], cfg.height, cfg.width, sc["shs"], 3, campos,
+                                          False, False)[1]
+        closer = None
+    else:
+        sys.path.insert(0, str(ROOT / "tests"))
+        import refbind
+        ref = refbind.RefDGR()
+
+        def render(view, proj, campos):
+            return ref.forward(sync=False, bg=bg, means3D=sc["means3D"], opacities=sc["opacities"], viewmatrix=view,
+                               projmatrix=proj, campos=campos, tan_fovx=tan[0], tan_fovy=tan[1], W=cfg.width,
+                               H=cfg.height, shs=sc["shs"], scales=sc["scales"], rotations=sc["rotations"])[1]
+        closer = ref.close
+
+    def resident_pass(_s):
+        for v in mine:
+            c = cams[v]
+            render(c.world_view_transform, c.full_proj_transform, c.camera_center)
+
+    img_host = [torch.empty(3, cfg.height, cfg.width).pin_memory() for _ in range(2)]
+    img_ev = [None, None]
+    cam_dev = [torch.empty(35, device=dev) for _ in range(2)]
+    cnt = {"n": 0}
+
+    def e2e_pass(_s):
+        for v in mine:
+            i = cnt["n"] & 1
+            cnt["n"] += 1
+            cd = cam_dev[i]
+            cd.copy_(cam_host[v], non_blocking=True)
+            img = render(cd[0:16].view(4, 4), cd[16:32].view(4, 4), cd[32:35])
+            if img_ev[i] is not None:
+                img_ev[i].synchronize()          # the host consumed (here: may overwrite) this pinned buffer
+            img_host[i].copy_(img, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(dev))
+            img_ev[i] = ev
+
+    for v in mine[:max(3, min(len(mine), 8))]:                    # warm-up (also sizes the binning workspaces)
+        c = cams[v]
+        render(c.world_view_transform, c.full_proj_transform, c.camera_center)
+    ms = timed_region(resident_pass, passes, world, dev)
+    e2e_pass(0)
+    ms_e2e = timed_region(e2e_pass, passes, world, dev)
+    if closer is not None:
+        closer()
+    total = nviews * passes
+    del sc
+    torch.cuda.empty_cache()
+    return {"metric": "render-only views/s at 6M Gaussians, SH3, 1920x1080 (C4), view-parallel",
+            "value": round(total / (ms * 1e-3), 2), "unit": "views/s", "n_gpus": world, "views": nviews,
+            "passes": passes, "scaling": "strong (64 views split over the ranks)",
+            "ms_per_view_per_gpu": round(ms / max(len(mine) * passes, 1), 4),
+            "e2e": {"value": round(total / (ms_e2e * 1e-3), 2), "unit": "views/s",
+                    "ms_per_view_per_gpu": round(ms_e2e / max(len(mine) * passes, 1), 4),
+                    "h2d_bytes_per_view": 35 * 4, "d2h_bytes_per_view": 3 * cfg.height * cfg.width * 4,
+                    "what": "camera block H2D + rendered image D2H to pinned host memory per view, double-buffered; "
+                            "no gather to rank 0 (every rank keeps / writes its own views, as render.py does per view)"},
+            "impl": impl}
 
 
 # ----------------------------------------------------------------------------------------- main
@@ -664,6 +896,13 @@ def main():
                     help="peer collective: use the view's radii to skip all-zero dL/dSH rows (exact; fewer NVLink "
                          "bytes but fewer loads in flight per CTA — slower at 2 GPUs, see DESIGN.md §7)")
     ap.add_argument("--multimem", action="store_true", help="peer collective: NVSwitch multimem.ld_reduce/st")
+    ap.add_argument("--dense-collective", action="store_true",
+                    help="peer collective: reduce the materialised 48-float dL/dsh rows (round-1 behaviour) instead of "
+                         "the factored SH gradient")
+    ap.add_argument("--no-render-only", action="store_true", help="skip the C4 render-only block")
+    ap.add_argument("--render-passes", type=int, default=2, help="timed passes over the 64 C4 views")
+    ap.add_argument("--blend-mode", default="strict", choices=["strict", "fast"],
+                    help="our arm: strict = expf (bit-exact n_contrib, the parity gate); fast = ex2.approx falloff")
     ap.add_argument("--allreduce", default="overlap", choices=["overlap", "blocking"],
                     help="N>1: overlap the gradient all-reduce of view k with the rasterization of view k+1")
     args = ap.parse_args()

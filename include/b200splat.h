@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define B200S_ABI_VERSION 1
+#define B200S_ABI_VERSION 2
 
 /* tile size is fixed by the reference (cuda_rasterizer/config.h:16-17) */
 #define B200S_BLOCK_X 16
@@ -160,6 +160,13 @@ typedef struct B200sBackwardArgs {
     float* dL_dconic;        /* [P,4] or NULL: (a, b, 0, c) as the reference lays it out */
     int32_t blend_mode;
     int32_t reserved;
+    /* Factored SH gradient (optional, shs path only). dL/dsh[k][c] of one view is the outer product
+     * basis_k(dir) * dL/dRGB[c] (backward.cu:20-139), so a view-parallel job need not move 48 floats per
+     * Gaussian: when non-NULL the backward writes the 3 post-clamp dL/dRGB floats per Gaussian to
+     * dL_dsh_factors[3*i .. 3*i+2] (zeros for culled Gaussians) and this view's camera centre to
+     * dL_dsh_factors[3*P .. 3*P+2]; b200s_sh_grad_reconstruct rebuilds (and sums over views) dL/dsh from such
+     * factor blocks bit-identically. dL_dsh may then be NULL (the 192-B rows are not written). */
+    float* dL_dsh_factors;   /* [3*P + 4] or NULL */
 } B200sBackwardArgs;
 
 size_t b200s_backward_workspace_size(int32_t P, int64_t num_rendered);
@@ -282,6 +289,13 @@ typedef struct B200sPeerReduceArgs {
     const void* radii;
     uint64_t sparse_offset_floats;   /* multiple of 4 */
     uint64_t vis_offset_bytes;       /* multiple of 4 */
+    /* All-gather region (optional, gather_floats == 0: none). Besides the summed prefix [0, n_floats) every
+     * buffer holds `world` slots of gather_floats floats at gather_offset_floats; rank r has filled slot r of
+     * ITS buffer before the call, and after it every rank's slot r holds rank r's data (each rank pulls the
+     * world-1 foreign slots over NVLink inside the same launch, between the same two barriers). Used for the
+     * factored SH gradient: 3 floats per Gaussian travel instead of 48 (see b200s_sh_grad_reconstruct). */
+    uint64_t gather_offset_floats;   /* multiple of 4, >= n_floats */
+    uint64_t gather_floats;          /* per-rank slot length, multiple of 4 */
 } B200sPeerReduceArgs;
 size_t b200s_peer_allreduce_flag_bytes(int32_t ctas, int32_t world);
 /* rows of the sparse tensor each rank owns (a multiple of the kernel's 1024-row work unit) and the size of
@@ -289,6 +303,23 @@ size_t b200s_peer_allreduce_flag_bytes(int32_t ctas, int32_t world);
 int64_t b200s_peer_allreduce_rows_per_rank(int32_t rows, int32_t world);
 size_t b200s_peer_allreduce_vis_bytes(int32_t rows, int32_t world);
 int b200s_peer_allreduce_sum_f32(const B200sPeerReduceArgs* args, b200s_stream_t stream);
+
+/* ---- factored SH gradient: dL/dsh summed over `views` factor blocks (the view-parallel ranks of one step after
+ *      the gather above, or several local views). Replaces moving / all-reducing the materialised dL/dsh rows
+ *      (48 of the 59 gradient floats per Gaussian; computeColorFromSH backward, backward.cu:20-139):
+ *          dL_dsh[i][k][c] = sum over v in view order of  fl( basis_k(normalize(means3D[i] - campos_v)) * g_v[i][c] )
+ *      where block v = factors + v*stride_floats holds g_v [P,3] followed by campos_v at float 3*P, exactly as
+ *      b200s_backward wrote them (dL_dsh_factors). Terms with g_v[i] == (0,0,0) are skipped, products and sums are
+ *      single fp32 roundings in view order, so the result equals the fixed-order sum of the per-view dL/dsh rows
+ *      b200s_backward would have written (same bits up to the sign of zero). Every element of dL_dsh is written. */
+typedef struct B200sShGradArgs {
+    int32_t P, D, M, views;
+    const float* means3D;        /* [P,3] */
+    const float* factors;        /* [views][stride_floats] */
+    uint64_t stride_floats;      /* >= 3*P + 4 */
+    float* dL_dsh;               /* [P,M,3], 16-byte aligned */
+} B200sShGradArgs;
+int b200s_sh_grad_reconstruct(const B200sShGradArgs* args, b200s_stream_t stream);
 
 /* ---- fused activation-backward + Adam + activation-forward for the replicated Gaussian
  *      parameters. Replaces, for the Gaussian tensors, autograd's chain
@@ -357,7 +388,7 @@ int b200s_l1_ssim_loss(const B200sLossArgs* args, b200s_stream_t stream);
 
 /* sizeof() of the ABI structs as compiled: 0 B200sHeader, 1 B200sForwardArgs,
  * 2 B200sBackwardArgs, 3 B200sIdxmapArgs, 4 B200sPeerReduceArgs,
- * 5 B200sAdamArgs, 6 B200sLossArgs. Bindings assert their own layout against it. */
+ * 5 B200sAdamArgs, 6 B200sLossArgs, 7 B200sShGradArgs. Bindings assert their own layout against it. */
 size_t b200s_sizeof(int32_t which);
 
 /* Library / build identification. */

@@ -33,7 +33,10 @@ NUM_FEATURES = 64
 # let the host return while sort + blend are still running, so the caller's loss / backward launches queue up behind
 # them instead of after a full-forward synchronise. Error bits raised by the later stages (look-back watchdogs) are
 # then reported by the NEXT forward call of the thread (no extra synchronisation); debug=True keeps the full check.
-config = {"deterministic": False, "optimistic": True, "growth": 1.25, "grad_out": None, "early_header": True}
+# blend_mode: 0 = strict (accurate expf, bit-exact n_contrib: the parity gate), 1 = fast (ex2.approx falloff in the forward
+# AND the backward blend, consistently; image within 1e-5, n_contrib may differ on a few pixels — tests/test_fast_mode_gpu.py).
+config = {"deterministic": False, "optimistic": True, "growth": 1.25, "grad_out": None, "early_header": True,
+          "blend_mode": 0}
 
 _tls = threading.local()
 _capacity_hint = {}   # (device index, P, W, H) -> last num_rendered
@@ -71,12 +74,63 @@ def _pinned_header() -> Tuple[torch.Tensor, "_lib.Header"]:
     return buf, _lib.Header.from_address(buf.data_ptr())
 
 
-def _pinned_header2() -> Tuple[torch.Tensor, "_lib.Header"]:
-    buf = getattr(_tls, "hdr2", None)
-    if buf is None:
-        buf = torch.zeros(C.sizeof(_lib.Header), dtype=torch.uint8).pin_memory()
-        _tls.hdr2 = buf
-    return buf, _lib.Header.from_address(buf.data_ptr())
+class _DeferredHeaderChecks:
+    """Error bits raised by the late stages of a forward (look-back watchdogs of expand / sort / ranges) are not
+    known when an early-header forward returns. Every such forward — and every backward, which consumes that state
+    — queues an asynchronous copy of the geometry header into a small ring of pinned slots; the slots whose copy
+    has completed are checked (without blocking) on entry to every later forward / backward call, and
+    `flush_errors()` checks all of them with a synchronisation (render-only callers, end of a run). The copy is
+    stream-ordered, so the geometry workspace need not be kept alive."""
+    SLOTS = 8
+
+    def __init__(self):
+        self.bufs = [torch.zeros(C.sizeof(_lib.Header), dtype=torch.uint8).pin_memory() for _ in range(self.SLOTS)]
+        self.events = [None] * self.SLOTS
+        self.where = [""] * self.SLOTS
+        self.n = 0
+
+    def _check(self, i):
+        self.events[i] = None
+        hdr = _lib.Header.from_address(self.bufs[i].data_ptr())
+        if hdr.error:
+            _raise_header_error(hdr.error, f" (raised by the late stages of an earlier {self.where[i]} call)")
+
+    def queue(self, lib, geom_ptr, dev, where):
+        i = self.n % self.SLOTS
+        self.n += 1
+        if self.events[i] is not None:
+            self.events[i].synchronize()
+            self._check(i)
+        _lib.check(lib.b200s_read_header(geom_ptr, self.bufs[i].data_ptr(), _stream(dev)), "b200s_read_header")
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(dev))
+        self.events[i], self.where[i] = ev, where
+
+    def poll(self, block=False):
+        for i in range(self.SLOTS):
+            ev = self.events[i]
+            if ev is None:
+                continue
+            if block:
+                ev.synchronize()
+            elif not ev.query():
+                continue
+            self._check(i)
+
+
+def _deferred() -> "_DeferredHeaderChecks":
+    d = getattr(_tls, "deferred", None)
+    if d is None:
+        d = _tls.deferred = _DeferredHeaderChecks()
+    return d
+
+
+def flush_errors() -> None:
+    """Wait for every queued header check of this thread and raise if a device-side watchdog fired."""
+    _deferred().poll(block=True)
+
+
+overflow_count = 0     # optimistic-capacity overflows since import (each one re-runs expand + sort + blend)
 
 
 def _raise_header_error(error: int, where: str = ""):
@@ -109,6 +163,7 @@ def _fill_forward_args(bg, means3D, colors, opacity, scales, rotations, scale_mo
     a.P, a.D, a.M, a.W, a.H = P, int(degree), int(M), int(W), int(H)
     a.tan_fovx, a.tan_fovy, a.scale_modifier = float(tan_fovx), float(tan_fovy), float(scale_modifier)
     a.prefiltered, a.debug = int(bool(prefiltered)), int(bool(debug))
+    a.blend_mode = int(config["blend_mode"])
     keep = [_f32c(t, dev) for t in (bg, means3D, sh, colors, opacity, scales, rotations, cov3D_precomp,
                                     viewmatrix, projmatrix, campos)]
     (a.background, a.means3D, a.shs, a.colors_precomp, a.opacities, a.scales, a.rotations, a.cov3D_precomp,
@@ -164,24 +219,18 @@ def _forward_impl(background, means3D, colors, opacity, scales, rotations, scale
         key = (dev.index, P, W, H)
         hint = _capacity_hint.get(key) if config["optimistic"] and not debug else None
         binning = None
+        deferred = _deferred()
+        deferred.poll()                                # late-stage error bits of earlier calls (non-blocking)
         if hint is not None and config["early_header"]:
             binning = alloc_bin(int(hint * config["growth"]) + 4096)
-            # deferred check of the previous forward's late-stage error bits rides on this call's one synchronisation
-            prev = getattr(_tls, "pending_geom", None)
-            buf2, hdr2 = _pinned_header2()
-            if prev is not None and prev.device == dev:
-                _lib.check(lib.b200s_read_header(prev.data_ptr(), buf2.data_ptr(), stream), "b200s_read_header")
             _lib.check(lib.b200s_forward_preprocess(C.byref(a), stream), "b200s_forward_preprocess")
             buf, hdr = _pinned_header()
             _lib.check(lib.b200s_read_header(geom.data_ptr(), buf.data_ptr(), stream), "b200s_read_header")
             ready = torch.cuda.Event()
             ready.record(torch.cuda.current_stream(dev))
             _lib.check(lib.b200s_forward_render(C.byref(a), stream), "b200s_forward_render")
+            deferred.queue(lib, geom.data_ptr(), dev, "forward")
             ready.synchronize()                        # scan done: sort + blend of this view are still in flight
-            _tls.pending_geom = geom
-            if prev is not None and prev.device == dev and hdr2.error:
-                _tls.pending_geom = None
-                _raise_header_error(hdr2.error, " (raised by the previous forward call)")
             if hdr.error:
                 _raise_header_error(hdr.error)
             if int(hdr.num_rendered) > int(a.bin_capacity):      # the device made stage 2 a no-op: redo it exactly
@@ -197,9 +246,16 @@ def _forward_impl(background, means3D, colors, opacity, scales, rotations, scale
             hdr = _read_header(lib, geom, dev)
         num_rendered = int(hdr.num_rendered)
         if binning is None:
+            if hint is not None:
+                global overflow_count
+                overflow_count += 1
             binning = alloc_bin(num_rendered)
             _lib.check(lib.b200s_forward_render(C.byref(a), stream), "b200s_forward_render")
-        _capacity_hint[key] = num_rendered
+            if hint is not None and config["early_header"]:
+                deferred.queue(lib, geom.data_ptr(), dev, "forward")
+        # capacity hint: running maximum with slow decay, so a loop that alternates small and large views does not
+        # overflow (and silently re-run expand + sort + blend) on every large one
+        _capacity_hint[key] = max(num_rendered, int(0.98 * _capacity_hint.get(key, 0)))
     return (num_rendered, out_color, radii, geom, binning, img), a, keep
 
 
@@ -229,6 +285,12 @@ def _backward_impl(background, means3D, radii, colors, scales, rotations, scale_
         g_means2D = torch.empty((P, 3), **f32)
         g_opacity = out("opacities", (P, 1))
         g_sh = out("shs", (P, M, 3)) if has_sh else torch.zeros((P, M, 3), **f32)
+        # factored SH gradient (parallel.PeerGradientAllReduce, factored=True): the backward emits 3 floats per
+        # Gaussian + the camera centre instead of the 48-float rows; g_sh is filled by the collective's reconstruction
+        sh_factors = pre.get("sh_factors") if has_sh else None
+        if sh_factors is not None and (sh_factors.numel() < 3 * P + 4 or sh_factors.dtype != torch.float32
+                                       or sh_factors.device != dev or not sh_factors.is_contiguous()):
+            raise RuntimeError("config['grad_out']['sh_factors'] must be a contiguous float32 tensor of >= 3*P+4 floats")
         g_scales = out("scales", (P, 3)) if has_sr else torch.zeros((P, 3), **f32)
         g_rot = out("rotations", (P, 4)) if has_sr else torch.zeros((P, 4), **f32)
         g_colors = torch.empty((P, NUM_CHANNELS), **f32) if (want_all or not has_sh) else None
@@ -240,6 +302,7 @@ def _backward_impl(background, means3D, radii, colors, scales, rotations, scale_
         a.tan_fovx, a.tan_fovy, a.scale_modifier = float(tan_fovx), float(tan_fovy), float(scale_modifier)
         a.debug = int(bool(debug))
         a.deterministic = int(bool(config["deterministic"]))
+        a.blend_mode = int(config["blend_mode"])
         keep = [_f32c(t, dev) for t in (background, means3D, sh, colors, scales, rotations, cov3D_precomp, viewmatrix,
                                         projmatrix, campos, dL_dout_color)]
         (a.background, a.means3D, a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp, a.viewmatrix,
@@ -255,12 +318,17 @@ def _backward_impl(background, means3D, radii, colors, scales, rotations, scale_
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         a.bwd_ws, a.bwd_bytes = ws.data_ptr(), nbytes
         a.dL_dmeans3D, a.dL_dmeans2D, a.dL_dopacity = g_means3D.data_ptr(), g_means2D.data_ptr(), g_opacity.data_ptr()
-        a.dL_dsh = g_sh.data_ptr() if has_sh else None
+        a.dL_dsh = g_sh.data_ptr() if (has_sh and sh_factors is None) else None
+        a.dL_dsh_factors = sh_factors.data_ptr() if sh_factors is not None else None
         a.dL_dscales = g_scales.data_ptr() if has_sr else None
         a.dL_drotations = g_rot.data_ptr() if has_sr else None
         a.dL_dcolors = g_colors.data_ptr() if g_colors is not None else None
         a.dL_dcov3D = g_cov3D.data_ptr() if g_cov3D is not None else None
+        deferred = _deferred()
+        deferred.poll()
         _lib.check(lib.b200s_backward(C.byref(a), _stream(dev)), "b200s_backward")
+        if config["optimistic"] and config["early_header"] and not debug:
+            deferred.queue(lib, geomBuffer.data_ptr(), dev, "forward/backward")   # the state this backward consumed
         del keep
     return g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot
 

@@ -62,6 +62,7 @@ class BackwardArgs(C.Structure):
         ("dL_dsh", C.c_void_p), ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p),
         ("dL_dcolors", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dconic", C.c_void_p),
         ("blend_mode", C.c_int32), ("reserved", C.c_int32),
+        ("dL_dsh_factors", C.c_void_p),
     ]
 
 
@@ -78,6 +79,7 @@ class IdxmapArgs(C.Structure):
 
 
 MAX_PEERS = 16
+ABI_VERSION = 2
 
 
 class PeerReduceArgs(C.Structure):
@@ -87,6 +89,14 @@ class PeerReduceArgs(C.Structure):
         ("rank", C.c_int32), ("world", C.c_int32), ("epoch", C.c_uint32), ("ctas", C.c_int32),
         ("use_multimem", C.c_int32), ("sparse_rows", C.c_int32),
         ("radii", C.c_void_p), ("sparse_offset_floats", C.c_uint64), ("vis_offset_bytes", C.c_uint64),
+        ("gather_offset_floats", C.c_uint64), ("gather_floats", C.c_uint64),
+    ]
+
+
+class ShGradArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("views", C.c_int32),
+        ("means3D", C.c_void_p), ("factors", C.c_void_p), ("stride_floats", C.c_uint64), ("dL_dsh", C.c_void_p),
     ]
 
 
@@ -161,6 +171,7 @@ SYMBOLS = [
     ("b200s_peer_allreduce_rows_per_rank", C.c_int64, [C.c_int32, C.c_int32]),
     ("b200s_peer_allreduce_vis_bytes", C.c_size_t, [C.c_int32, C.c_int32]),
     ("b200s_peer_allreduce_sum_f32", C.c_int, [C.POINTER(PeerReduceArgs), C.c_void_p]),
+    ("b200s_sh_grad_reconstruct", C.c_int, [C.POINTER(ShGradArgs), C.c_void_p]),
     ("b200s_adam_step", C.c_int, [C.POINTER(AdamArgs), C.c_void_p]),
     ("b200s_loss_workspace_size", C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     ("b200s_l1_ssim_loss", C.c_int, [C.POINTER(LossArgs), C.c_void_p]),
@@ -191,9 +202,10 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = restype
         fn.argtypes = argtypes
-    if lib.b200s_abi_version() != 1:
+    if lib.b200s_abi_version() != ABI_VERSION:
         raise RuntimeError("libb200splat.so ABI version mismatch")
-    for which, struct in enumerate((Header, ForwardArgs, BackwardArgs, IdxmapArgs, PeerReduceArgs, AdamArgs, LossArgs)):
+    for which, struct in enumerate((Header, ForwardArgs, BackwardArgs, IdxmapArgs, PeerReduceArgs, AdamArgs, LossArgs,
+                                   ShGradArgs)):
         if lib.b200s_sizeof(which) != C.sizeof(struct):
             raise RuntimeError(f"ctypes layout of {struct.__name__} does not match the library")
     _lib = lib

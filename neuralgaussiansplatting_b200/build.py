@@ -19,8 +19,9 @@ OBJ_DIR = PKG_DIR / "_obj"
 LIB_PATH = PKG_DIR / "libb200splat.so"
 
 SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "blend_fwd.cu", "blend_bwd.cu", "preprocess_bwd.cu", "idxmap.cu",
-           "peer_reduce.cu", "optimizer.cu", "loss.cu"]
-HEADERS = [CSRC / "common.cuh", CSRC / "kernels.cuh", CSRC / "blend_common.cuh", INCLUDE / "b200splat.h"]
+           "peer_reduce.cu", "sh_reconstruct.cu", "optimizer.cu", "loss.cu"]
+HEADERS = [CSRC / "common.cuh", CSRC / "kernels.cuh", CSRC / "blend_common.cuh", CSRC / "sh_grad.cuh",
+           INCLUDE / "b200splat.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

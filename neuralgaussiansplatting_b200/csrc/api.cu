@@ -170,6 +170,7 @@ size_t b200s_sizeof(int32_t which) {
         case 4: return sizeof(B200sPeerReduceArgs);
         case 5: return sizeof(B200sAdamArgs);
         case 6: return sizeof(B200sLossArgs);
+        case 7: return sizeof(B200sShGradArgs);
         default: return 0;
     }
 }
@@ -288,13 +289,14 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
     const int passes = sort_num_passes(d.tiles);
     const int final_buf = passes & 1;
 
-    ProfScope* misc = new ProfScope(B200S_STAGE_MISC, stream);
-    if (a->deterministic) {
-        B200S_CUDA_OK(cudaMemsetAsync(ws.partial, 0, sizeof(float) * ACC_STRIDE * (size_t)(a->num_rendered > 0 ? a->num_rendered : 1), stream));
-    } else {
-        B200S_CUDA_OK(cudaMemsetAsync(ws.accum, 0, sizeof(float) * ACC_STRIDE * (size_t)a->P, stream));
+    {
+        ProfScope misc(B200S_STAGE_MISC, stream);
+        if (a->deterministic) {
+            B200S_CUDA_OK(cudaMemsetAsync(ws.partial, 0, sizeof(float) * ACC_STRIDE * (size_t)(a->num_rendered > 0 ? a->num_rendered : 1), stream));
+        } else {
+            B200S_CUDA_OK(cudaMemsetAsync(ws.accum, 0, sizeof(float) * ACC_STRIDE * (size_t)a->P, stream));
+        }
     }
-    delete misc;
     if (a->num_rendered > 0) {
         BlendBwdParams b;
         b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;
@@ -321,7 +323,7 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
     p.accum = a->deterministic ? nullptr : ws.accum;
     p.partial = a->deterministic ? ws.partial : nullptr;
     p.dL_dmeans3D = a->dL_dmeans3D; p.dL_dmeans2D = a->dL_dmeans2D; p.dL_dopacity = a->dL_dopacity;
-    p.dL_dsh = a->dL_dsh; p.dL_dscales = a->dL_dscales; p.dL_drotations = a->dL_drotations;
+    p.dL_dsh = a->dL_dsh; p.dL_dsh_factors = a->shs ? a->dL_dsh_factors : nullptr; p.dL_dscales = a->dL_dscales; p.dL_drotations = a->dL_drotations;
     p.dL_dcolors = a->dL_dcolors; p.dL_dcov3D = a->dL_dcov3D; p.dL_dconic = a->dL_dconic;
     int rc;
     {
@@ -382,8 +384,20 @@ extern "C" int b200s_peer_allreduce_sum_f32(const B200sPeerReduceArgs* a, b200s_
         if (a->sparse_rows <= 0 || (a->sparse_offset_floats & 3u) || (a->vis_offset_bytes & 3u)) return B200S_E_BADARG;
         if (a->sparse_offset_floats + (uint64_t)a->sparse_rows * 48u > a->n_floats) return B200S_E_BADARG;
     }
-    if (a->n_floats == 0 || a->world == 1) return 0;
+    if ((a->gather_floats & 3u) || (a->gather_offset_floats & 3u)) return B200S_E_BADARG;
+    if (a->gather_floats && a->gather_offset_floats < a->n_floats) return B200S_E_BADARG;
+    if ((a->n_floats == 0 && a->gather_floats == 0) || a->world == 1) return 0;
     return launch_peer_allreduce(*a, (cudaStream_t)stream_);
+}
+
+extern "C" int b200s_sh_grad_reconstruct(const B200sShGradArgs* a, b200s_stream_t stream_) {
+    if (!a || a->P < 0 || a->views < 1 || a->views > B200S_MAX_PEERS || a->D < 0 || a->D > 3) return B200S_E_BADARG;
+    if (a->P == 0) return 0;
+    if (!a->means3D || !a->factors || !a->dL_dsh) return B200S_E_BADARG;
+    if (a->M < (a->D + 1) * (a->D + 1) || a->M > 16) return B200S_E_BADARG;
+    if (a->stride_floats < 3ull * (uint64_t)a->P + 4ull) return B200S_E_BADARG;
+    if ((uintptr_t)a->dL_dsh & 15u) return B200S_E_BADARG;
+    return launch_sh_grad_reconstruct(*a, (cudaStream_t)stream_);
 }
 
 extern "C" int b200s_adam_step(const B200sAdamArgs* a, b200s_stream_t stream_) {

@@ -639,14 +639,8 @@ static bool rank_by_match(int which, int pass) {
     return (mask >> (which * 4 + pass)) & 1;
 }
 static int set_sort_attr() {
-    static bool attr_set = false;
-    if (!attr_set) {
-        B200S_CUDA_OK(cudaFuncSetAttribute(sort_onesweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)SORT_SMEM));
-        B200S_CUDA_OK(cudaFuncSetAttribute(sort_onesweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)SORT_SMEM));
-        attr_set = true;
-    }
+    B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+    B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
     return 0;
 }
 

@@ -1,6 +1,7 @@
 // Shared definitions for the b200splat kernels (sm_100a only).
 #pragma once
 
+#include <atomic>
 #include <cstdint>
 #include <cstdio>
 #include <cuda_runtime.h>
@@ -201,6 +202,20 @@ enum { ERR_LOOKBACK_TIMEOUT = 1u, ERR_PREFILTERED = 2u };
             _e = cudaStreamSynchronize(stream);               \
             if (_e != cudaSuccess) return (int)_e;            \
         }                                                     \
+    } while (0)
+
+// cudaFuncSetAttribute applies to the CURRENT device only, so "done once" has to be tracked per device (a
+// process may drive several GPUs, and several host threads may race here): one atomic flag per (call site,
+// device). Returns a cudaError_t as int.
+#define B200S_SET_FUNC_ATTR_ONCE(kernel, attr, value)                                            \
+    do {                                                                                         \
+        static std::atomic<unsigned char> _done[64];                                             \
+        int _dev = 0;                                                                            \
+        B200S_CUDA_OK(cudaGetDevice(&_dev));                                                     \
+        if (_dev < 0 || _dev >= 64 || !_done[_dev].load(std::memory_order_acquire)) {            \
+            B200S_CUDA_OK(cudaFuncSetAttribute(kernel, attr, value));                            \
+            if (_dev >= 0 && _dev < 64) _done[_dev].store(1, std::memory_order_release);         \
+        }                                                                                        \
     } while (0)
 
 #ifdef __CUDACC__

@@ -78,6 +78,7 @@ struct PreprocessBwdParams {
     float* dL_dmeans2D;
     float* dL_dopacity;
     float* dL_dsh;
+    float* dL_dsh_factors;   // [3P + 4] or NULL (factored SH gradient)
     float* dL_dscales;
     float* dL_drotations;
     float* dL_dcolors;
@@ -106,6 +107,7 @@ int launch_blend_fwd(const BlendFwdParams& p, int nw, cudaStream_t stream);
 int launch_blend_bwd(const BlendBwdParams& p, int nw, cudaStream_t stream);
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream);
 int launch_peer_allreduce(const B200sPeerReduceArgs& a, cudaStream_t stream);
+int launch_sh_grad_reconstruct(const B200sShGradArgs& a, cudaStream_t stream);
 int launch_adam_step(const B200sAdamArgs& a, cudaStream_t stream);
 size_t loss_workspace_size(int C, int H, int W);
 int launch_l1_ssim(const B200sLossArgs& a, cudaStream_t stream);

@@ -47,6 +47,8 @@ struct PeerReduceParams {
     int rows_per;          // rows owned per rank, a multiple of PR_CHUNK
     size_t sparse_off4;    // first float4 of the row-structured tensor (PR_ROW4 float4 per row)
     size_t vis_off;        // byte offset of the visibility array from bufs[r]
+    // all-gather region: slot r (gslot4 float4) at goff4 + r*gslot4 of every buffer ends up holding rank r's data
+    size_t goff4, gslot4;
 };
 
 constexpr unsigned long long PR_BARRIER_TIMEOUT_NS = 60ull * 1000000000ull;   // peers start within a minute or never
@@ -119,6 +121,38 @@ __device__ __forceinline__ void peer_barrier(const PeerReduceParams& p, int phas
         }
     }
     __syncthreads();
+}
+
+// All-gather of the per-rank slots (factored SH gradient: 3 floats per Gaussian instead of the 48-float row):
+// this rank pulls slot r from rank r's buffer into slot r of its own, for every peer r. Loads of up to eight
+// peers x UG elements are in flight per thread before the first store.
+__device__ __forceinline__ void peer_gather_slots(const PeerReduceParams& p, int world) {
+    constexpr int UG = 2;
+    const size_t stride = (size_t)gridDim.x * PR_THREADS;
+    float4* mine = p.bufs[p.rank] + p.goff4;
+    for (int r0 = 0; r0 < world; r0 += 8) {
+        for (size_t i0 = (size_t)blockIdx.x * PR_THREADS + threadIdx.x; i0 < p.gslot4; i0 += stride * UG) {
+            float4 v[UG][8];
+#pragma unroll
+            for (int u = 0; u < UG; ++u) {
+                const size_t i = i0 + u * stride;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const int r = r0 + q;
+                    if (r < world && r != p.rank && i < p.gslot4) v[u][q] = ld_peer(p.bufs[r] + p.goff4 + (size_t)r * p.gslot4 + i);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UG; ++u) {
+                const size_t i = i0 + u * stride;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const int r = r0 + q;
+                    if (r < world && r != p.rank && i < p.gslot4) st_peer(mine + (size_t)r * p.gslot4 + i, v[u][q]);
+                }
+            }
+        }
+    }
 }
 
 template <int WORLD, bool MULTIMEM, bool SPARSE>
@@ -206,6 +240,8 @@ peer_allreduce_kernel(const __grid_constant__ PeerReduceParams p) {
         }
     }
 
+    if (p.gslot4 != 0) peer_gather_slots(p, world);
+
     if constexpr (SPARSE && WORLD > 0) {
         __shared__ uint32_t smask[PR_CHUNK / 4];        // one byte per row: bit r = visible on rank r
         constexpr int US = WORLD <= 4 ? 4 : 2;
@@ -273,6 +309,8 @@ int launch_peer_allreduce(const B200sPeerReduceArgs& a, cudaStream_t stream) {
     p.mc = (float4*)a.multicast_buf;
     p.n4 = (size_t)(a.n_floats / 4);
     p.rank = a.rank; p.world = a.world; p.epoch = a.epoch;
+    p.goff4 = (size_t)(a.gather_offset_floats / 4);
+    p.gslot4 = (size_t)(a.gather_floats / 4);
     const int ctas = a.ctas;
     if (a.use_multimem) return launch_pr<0, true>(p, ctas, stream);
     if (a.radii && a.sparse_rows > 0) {

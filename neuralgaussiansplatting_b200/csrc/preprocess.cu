@@ -235,13 +235,8 @@ int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream) {
     const bool sh16 = p.colors_precomp == nullptr && p.M == 16 &&
                       (reinterpret_cast<uintptr_t>(p.shs) % 16 == 0);
     if (sh16) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            B200S_CUDA_OK(cudaFuncSetAttribute(preprocess_fwd_kernel<true>,
-                                               cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               (int)PRE_SMEM_SH16));
-            attr_set = true;
-        }
+        B200S_SET_FUNC_ATTR_ONCE(preprocess_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)PRE_SMEM_SH16);
         count_launch();
         preprocess_fwd_kernel<true><<<blocks, PRE_THREADS, PRE_SMEM_SH16, stream>>>(p);
     } else {

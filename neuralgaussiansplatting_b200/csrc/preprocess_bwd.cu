@@ -11,6 +11,7 @@
 
 #include <cstdlib>
 #include "kernels.cuh"
+#include "sh_grad.cuh"
 
 namespace b200s {
 
@@ -20,13 +21,10 @@ constexpr int PB_ROW_FLOATS = 48;
 constexpr int PB_ROW_PAD = 52;
 constexpr size_t PB_SMEM_SH16 = (size_t)PB_THREADS * PB_ROW_PAD * sizeof(float);
 
-__device__ const float bSH_C0 = 0.28209479177387814f;
-__device__ const float bSH_C1 = 0.4886025119029199f;
-__device__ const float bSH_C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
-                                    -1.0925484305920792f, 0.5462742152960396f};
-__device__ const float bSH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
-                                    0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
-                                    -0.5900435899266435f};
+#define bSH_C0 gSH_C0
+#define bSH_C1 gSH_C1
+#define bSH_C2 gSH_C2
+#define bSH_C3 gSH_C3
 
 __device__ __forceinline__ void pb_cp_async16(void* smem_dst, const void* gmem_src) {
     uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
@@ -43,34 +41,26 @@ __device__ __forceinline__ float dot(float3 a, float3 b) { return a.x * b.x + a.
 template <typename Get, typename Put>
 __device__ __forceinline__ float3 sh_backward(int deg, float x, float y, float z, float3 dRGB, Get get, Put put) {
     float3 dx = f3(0, 0, 0), dy = f3(0, 0, 0), dz = f3(0, 0, 0);
-    put(0, bSH_C0 * dRGB);
+    // dL/dsh[k] = basis_k * dL/dRGB: single-rounding products of the shared basis (sh_grad.cuh), which the
+    // factored-gradient reconstruction reproduces bit for bit
+    float bas[16];
+    sh_basis(deg, x, y, z, bas);
+    const int ncoef = (deg + 1) * (deg + 1);
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        if (k < ncoef) put(k, f3(fmul(bas[k], dRGB.x), fmul(bas[k], dRGB.y), fmul(bas[k], dRGB.z)));
     if (deg > 0) {
-        put(1, (-bSH_C1 * y) * dRGB);
-        put(2, (bSH_C1 * z) * dRGB);
-        put(3, (-bSH_C1 * x) * dRGB);
         const float3 s1 = get(1), s2 = get(2), s3 = get(3);
         dx = (-bSH_C1) * s3;
         dy = (-bSH_C1) * s1;
         dz = bSH_C1 * s2;
         if (deg > 1) {
             const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-            put(4, (bSH_C2[0] * xy) * dRGB);
-            put(5, (bSH_C2[1] * yz) * dRGB);
-            put(6, (bSH_C2[2] * (2.f * zz - xx - yy)) * dRGB);
-            put(7, (bSH_C2[3] * xz) * dRGB);
-            put(8, (bSH_C2[4] * (xx - yy)) * dRGB);
             const float3 s4 = get(4), s5 = get(5), s6 = get(6), s7 = get(7), s8 = get(8);
             dx = dx + (bSH_C2[0] * y) * s4 + (bSH_C2[2] * 2.f * -x) * s6 + (bSH_C2[3] * z) * s7 + (bSH_C2[4] * 2.f * x) * s8;
             dy = dy + (bSH_C2[0] * x) * s4 + (bSH_C2[1] * z) * s5 + (bSH_C2[2] * 2.f * -y) * s6 + (bSH_C2[4] * 2.f * -y) * s8;
             dz = dz + (bSH_C2[1] * y) * s5 + (bSH_C2[2] * 2.f * 2.f * z) * s6 + (bSH_C2[3] * x) * s7;
             if (deg > 2) {
-                put(9, (bSH_C3[0] * y * (3.f * xx - yy)) * dRGB);
-                put(10, (bSH_C3[1] * xy * z) * dRGB);
-                put(11, (bSH_C3[2] * y * (4.f * zz - xx - yy)) * dRGB);
-                put(12, (bSH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dRGB);
-                put(13, (bSH_C3[4] * x * (4.f * zz - xx - yy)) * dRGB);
-                put(14, (bSH_C3[5] * z * (xx - yy)) * dRGB);
-                put(15, (bSH_C3[6] * x * (xx - 3.f * yy)) * dRGB);
                 const float3 s9 = get(9), s10 = get(10), s11 = get(11), s12 = get(12), s13 = get(13),
                              s14 = get(14), s15 = get(15);
                 dx = dx + (bSH_C3[0] * 3.f * 2.f * xy) * s9 + (bSH_C3[1] * yz) * s10 + (bSH_C3[2] * -2.f * xy) * s11 +
@@ -267,19 +257,25 @@ preprocess_bwd_kernel(const __grid_constant__ PreprocessBwdParams p) {
             g_rot.w = 2 * qr * (t01 - t10) + 2 * qx * (t20 + t02) + 2 * qy * (t12 + t21) - 4 * qz * (t11 + t00);
         }
         if (use_sh) {
-            dir_orig = f3(mx - p.campos[0], my - p.campos[1], mz - p.campos[2]);
-            const float len = sqrtf(dot(dir_orig, dir_orig));
-            dir = f3(dir_orig.x / len, dir_orig.y / len, dir_orig.z / len);
+            sh_view_dir(mx, my, mz, p.campos[0], p.campos[1], p.campos[2], dir_orig, dir);
             clamp_bits = p.clamped[idx];
         }
     }
 
     // ---- SH backward + dL/dsh output (all rows of the block are written)
-    if (use_sh && p.dL_dsh != nullptr) {
+    const bool write_rows = p.dL_dsh != nullptr;
+    if (use_sh && (write_rows || p.dL_dsh_factors != nullptr)) {
         float3 dRGB = g_col;
         if (clamp_bits & 1u) dRGB.x = 0.f;
         if (clamp_bits & 2u) dRGB.y = 0.f;
         if (clamp_bits & 4u) dRGB.z = 0.f;
+        if (p.dL_dsh_factors != nullptr) {
+            // factored SH gradient: the 3-float factor of this view's rank-1 dL/dsh row (+ the camera centre)
+            if (in_range) {
+                p.dL_dsh_factors[3 * idx] = dRGB.x; p.dL_dsh_factors[3 * idx + 1] = dRGB.y; p.dL_dsh_factors[3 * idx + 2] = dRGB.z;
+            }
+            if (blockIdx.x == 0 && tid < 4) p.dL_dsh_factors[3 * (int64_t)p.P + tid] = tid < 3 ? p.campos[tid] : 0.f;
+        }
         if (SH16) {
             if (vis_mask != 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
             __syncwarp();
@@ -293,12 +289,14 @@ preprocess_bwd_kernel(const __grid_constant__ PreprocessBwdParams p) {
                 }
             }
             // the row now lives in registers: reuse its shared-memory slot for dL/dsh
+            if (write_rows) {
 #pragma unroll
-            for (int k = 0; k < 12; ++k) reinterpret_cast<float4*>(row)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int k = 0; k < 12; ++k) reinterpret_cast<float4*>(row)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
             if (visible) {
                 const float3 dd = sh_backward(
                     p.D, dir.x, dir.y, dir.z, dRGB, [&](int k) { return f3(v[3 * k], v[3 * k + 1], v[3 * k + 2]); },
-                    [&](int k, float3 g) { row[3 * k] = g.x; row[3 * k + 1] = g.y; row[3 * k + 2] = g.z; });
+                    [&](int k, float3 g) { if (write_rows) { row[3 * k] = g.x; row[3 * k + 1] = g.y; row[3 * k + 2] = g.z; } });
                 // dnormvdv (auxiliary.h:107-117)
                 const float3 vv = dir_orig;
                 const float sum2 = vv.x * vv.x + vv.y * vv.y + vv.z * vv.z;
@@ -308,25 +306,28 @@ preprocess_bwd_kernel(const __grid_constant__ PreprocessBwdParams p) {
                 g_mean.z += (-vv.x * vv.z * dd.x - vv.y * vv.z * dd.y + (sum2 - vv.z * vv.z) * dd.z) * inv;
             }
             __syncwarp();
-            // coalesced write-back of the warp's 32 rows (6 KB contiguous)
-            const int64_t gbase = ((int64_t)blockIdx.x * PB_THREADS + warp * 32);
-            float* gdst = p.dL_dsh + gbase * PB_ROW_FLOATS;
+            if (write_rows) {
+                // coalesced write-back of the warp's 32 rows (6 KB contiguous)
+                const int64_t gbase = ((int64_t)blockIdx.x * PB_THREADS + warp * 32);
+                float* gdst = p.dL_dsh + gbase * PB_ROW_FLOATS;
 #pragma unroll
-            for (int it = 0; it < 12; ++it) {
-                const int c = it * 32 + lane;
-                const int r = c / 12;
-                const int ch = c - r * 12;
-                if (gbase + r < p.P)
-                    reinterpret_cast<float4*>(gdst)[c] = *reinterpret_cast<const float4*>(tile + r * PB_ROW_PAD + ch * 4);
+                for (int it = 0; it < 12; ++it) {
+                    const int c = it * 32 + lane;
+                    const int r = c / 12;
+                    const int ch = c - r * 12;
+                    if (gbase + r < p.P)
+                        reinterpret_cast<float4*>(gdst)[c] = *reinterpret_cast<const float4*>(tile + r * PB_ROW_PAD + ch * 4);
+                }
             }
         } else if (in_range) {
-            float* out = p.dL_dsh + (int64_t)idx * p.M * 3;
-            for (int k = 0; k < p.M * 3; ++k) out[k] = 0.f;
+            float* out = write_rows ? p.dL_dsh + (int64_t)idx * p.M * 3 : nullptr;
+            if (write_rows)
+                for (int k = 0; k < p.M * 3; ++k) out[k] = 0.f;
             if (visible) {
                 const float* sh = p.shs + (int64_t)idx * p.M * 3;
                 const float3 dd = sh_backward(
                     p.D, dir.x, dir.y, dir.z, dRGB, [&](int k) { return f3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]); },
-                    [&](int k, float3 g) { out[3 * k] = g.x; out[3 * k + 1] = g.y; out[3 * k + 2] = g.z; });
+                    [&](int k, float3 g) { if (write_rows) { out[3 * k] = g.x; out[3 * k + 1] = g.y; out[3 * k + 2] = g.z; } });
                 const float3 vv = dir_orig;
                 const float sum2 = vv.x * vv.x + vv.y * vv.y + vv.z * vv.z;
                 const float inv = 1.0f / sqrtf(sum2 * sum2 * sum2);
@@ -357,18 +358,15 @@ preprocess_bwd_kernel(const __grid_constant__ PreprocessBwdParams p) {
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream) {
     if (p.P <= 0) return 0;
     const int blocks = (p.P + PB_THREADS - 1) / PB_THREADS;
-    const bool sh16 = p.shs != nullptr && p.colors_precomp == nullptr && p.dL_dsh != nullptr && p.M == 16 &&
+    const bool sh16 = p.shs != nullptr && p.colors_precomp == nullptr &&
+                      (p.dL_dsh != nullptr || p.dL_dsh_factors != nullptr) && p.M == 16 &&
                       (reinterpret_cast<uintptr_t>(p.shs) % 16 == 0) &&
                       (reinterpret_cast<uintptr_t>(p.dL_dsh) % 16 == 0);
     if (sh16) {
         static int minb = [] { const char* v = getenv("B200S_PB_MINB"); return v && *v ? atoi(v) : 3; }();
         auto kern = minb >= 4 ? preprocess_bwd_kernel<true, 4> : minb == 3 ? preprocess_bwd_kernel<true, 3>
                                                                             : preprocess_bwd_kernel<true, 2>;
-        static bool attr_set = false;
-        if (!attr_set) {
-            B200S_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PB_SMEM_SH16));
-            attr_set = true;
-        }
+        B200S_SET_FUNC_ATTR_ONCE(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PB_SMEM_SH16);
         count_launch();
         kern<<<blocks, PB_THREADS, PB_SMEM_SH16, stream>>>(p);
     } else {

@@ -112,6 +112,82 @@ class GradientAllReduce:
         return self._done is not None or bool(self._works)
 
 
+class FlatGradientAllReduce:
+    """ONE ncclAllReduce per step over a flat buffer that holds the five gradient tensors (gradient_layout) — the
+    strongest plain-NCCL formulation (no per-tensor buckets, no staging copy: the backward writes into views of the
+    buffer through `_C.config["grad_out"]`, or a reference binding zero-fills and accumulates into them). Buffers
+    rotate so the reduce of view k can overlap view k+1. Same start()/wait() protocol as GradientAllReduce; used by
+    both bench arms as the NCCL comparison / reference-arm collective."""
+
+    def __init__(self, P: int, sh_coeffs: int = 16, device=None, group=None, n_buffers: int = 2):
+        self.group = group
+        self.layout, self.n_floats = gradient_layout(P, sh_coeffs)
+        self.device = torch.device(device if device is not None else "cpu")
+        self._flat = [torch.zeros(self.n_floats, dtype=torch.float32, device=self.device) for _ in range(n_buffers)]
+        self.n_buffers = int(n_buffers)
+        self._cur = -1
+        self._stream: Optional[torch.cuda.Stream] = None
+        self._done: Optional[torch.cuda.Event] = None
+        self._work = None
+        self._copy_back = None
+
+    def _views(self, i: int) -> Dict[str, torch.Tensor]:
+        out = {}
+        for name, (off, shape) in self.layout.items():
+            n = 1
+            for d in shape:
+                n *= d
+            out[name] = self._flat[i][off:off + n].view(shape)
+        return out
+
+    def grad_out(self) -> Dict[str, torch.Tensor]:
+        self._cur = (self._cur + 1) % self.n_buffers
+        return self._views(self._cur)
+
+    def start(self, grads: Optional[Dict[str, torch.Tensor]] = None, **_unused) -> None:
+        if not dist.is_initialized() or dist.get_world_size(self.group) == 1:
+            return
+        if self._cur < 0:
+            self._cur = 0
+        views, flat = self._views(self._cur), self._flat[self._cur]
+        self._copy_back = None
+        if grads is not None:
+            stray = {k: g for k, g in grads.items() if g is not None and k in views
+                     and g.data_ptr() != views[k].data_ptr()}
+            if stray:
+                for k, g in stray.items():
+                    views[k].copy_(g.reshape(views[k].shape))
+                self._copy_back = (stray, views)
+        if flat.is_cuda:
+            if self._stream is None:
+                self._stream = torch.cuda.Stream(device=flat.device)
+            ready = torch.cuda.Event()
+            ready.record(torch.cuda.current_stream(flat.device))
+            self._stream.wait_event(ready)
+            with torch.cuda.stream(self._stream):
+                dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+                self._done = torch.cuda.Event()
+                self._done.record(self._stream)
+        else:
+            self._work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+
+    def wait(self) -> None:
+        if self._work is not None:
+            self._work.wait()
+            self._work = None
+        if self._done is not None:
+            torch.cuda.current_stream().wait_event(self._done)
+            self._done = None
+        if self._copy_back is not None:
+            stray, views = self._copy_back
+            for k, g in stray.items():
+                g.copy_(views[k].reshape(g.shape))
+            self._copy_back = None
+
+    def pending(self) -> bool:
+        return self._done is not None or self._work is not None
+
+
 def gradient_layout(P: int, sh_coeffs: int = 16, align_floats: int = 64):
     """Offsets (in floats) of the five gradient tensors inside one flat peer buffer, each sub-tensor starting on a
     256-byte boundary (preprocess_bwd stores dL/dsh rows as 16-byte vectors). Returns ({name: (offset, shape)},
@@ -235,7 +311,7 @@ class PeerGradientAllReduce:
     AUTO_CTAS = {2: 16, 3: 16, 4: 12}
 
     def __init__(self, P: int, sh_coeffs: int = 16, device=None, group=None, n_buffers: int = 2, ctas: int = 0,
-                 multimem: bool = False, backend: str = "auto"):
+                 multimem: bool = False, backend: str = "auto", factored: bool = True):
         from . import _lib
         self._libmod = _lib
         self._lib = _lib.load()
@@ -245,10 +321,19 @@ class PeerGradientAllReduce:
             raise ValueError(f"at most {_lib.MAX_PEERS} peers")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.layout, self.n_floats = gradient_layout(P, sh_coeffs)
+        # Factored SH gradient (default): within one view dL/dsh is the outer product basis(dir) x dL/dRGB, so the
+        # backward emits 3 floats per Gaussian (+ its camera centre) into this rank's slot of a gather region behind
+        # the five tensors; the collective sums only the 11 dense floats, gathers the slots, and
+        # b200s_sh_grad_reconstruct rebuilds the summed 48-float rows locally — bit-identical to reducing the rows,
+        # with 2.5x fewer NVLink bytes (csrc/sh_reconstruct.cu).
+        self.factored = bool(factored)
+        self.dense_floats = self.layout["shs"][0]                      # means3D, opacities, scales, rotations
+        self.slot_floats = -(-(3 * int(P) + 4) // 64) * 64
+        self.gather_floats_total = self.world * self.slot_floats if self.factored else 0
         self.n_buffers = int(n_buffers)
         self.ctas = int(ctas) if ctas and ctas > 0 else self.AUTO_CTAS.get(self.world, 8)
         self.flag_bytes = -(-int(self._lib.b200s_peer_allreduce_flag_bytes(self.ctas, self.world)) // 256) * 256
-        self.buf_bytes = self.n_floats * 4
+        self.buf_bytes = (self.n_floats + self.gather_floats_total) * 4
         self.P, self.sh_coeffs = int(P), int(sh_coeffs)
         # one visibility byte per Gaussian next to every buffer (sparse tail of the collective, see start())
         self.vis_bytes = -(-int(self._lib.b200s_peer_allreduce_vis_bytes(self.P, self.world)) // 256) * 256
@@ -266,6 +351,7 @@ class PeerGradientAllReduce:
         self._stream = torch.cuda.Stream(device=self.device, priority=-1)
         self._done: Optional[torch.cuda.Event] = None
         self._copy_back = None
+        self._factors_fresh = False
 
     # ---- buffers
     def _views(self, i: int) -> Dict[str, torch.Tensor]:
@@ -278,14 +364,27 @@ class PeerGradientAllReduce:
             out[name] = flat[off:off + n].view(shape)
         return out
 
+    def _factor_slot(self, i: int, r: int) -> torch.Tensor:
+        off = self.n_floats + r * self.slot_floats
+        return self._flat[i][off:off + self.slot_floats]
+
     def grad_out(self) -> Dict[str, torch.Tensor]:
-        """Rotate to the next buffer and return fresh views of it (install as `_C.config["grad_out"]`)."""
+        """Rotate to the next buffer and return fresh views of it (install as `_C.config["grad_out"]`). In factored
+        mode the dict carries "sh_factors" (this rank's gather slot): the backward then writes 3 floats per Gaussian
+        there instead of the dL/dsh rows, and the "shs" view is filled by the collective."""
         self._cur = (self._cur + 1) % self.n_buffers
-        return self._views(self._cur)
+        out = self._views(self._cur)
+        if self.factored:
+            out["sh_factors"] = self._factor_slot(self._cur, self.rank)
+            self._factors_fresh = True
+        return out
 
     # ---- collective
-    def start(self, grads: Optional[Dict[str, torch.Tensor]] = None, radii: Optional[torch.Tensor] = None) -> None:
-        """Launch the collective for the current buffer. `radii` (int32[P], this rank's forward output for the
+    def start(self, grads: Optional[Dict[str, torch.Tensor]] = None, radii: Optional[torch.Tensor] = None,
+              means3D: Optional[torch.Tensor] = None, sh_degree: int = 3, factored: Optional[bool] = None) -> None:
+        """Launch the collective for the current buffer. Factored mode (the backward of THIS step wrote its factors
+        through grad_out(); every rank must take the same mode) needs `means3D` (the replicated [P,3] positions the
+        views were rendered from) and the active `sh_degree` for the local reconstruction of dL/dsh. `radii` (int32[P], this rank's forward output for the
         view the gradients belong to) enables the visibility-sparse SH tail: rows with radii <= 0 are all-zero
         here, so owners skip them — same bits as the dense sum, less NVLink traffic. Only pass it when the
         buffer holds the gradients of exactly that one view (not a local accumulation over several views)."""
@@ -293,16 +392,25 @@ class PeerGradientAllReduce:
             self._cur = 0
         views = self._views(self._cur)
         self._copy_back = None
+        use_factored = self.factored and self._factors_fresh if factored is None else bool(factored)
+        if use_factored and not (self.factored and self._factors_fresh):
+            raise RuntimeError("factored collective: this step's backward did not write its factors (grad_out())")
+        if use_factored and (means3D is None or means3D.shape != (self.P, 3) or not means3D.is_contiguous()
+                             or means3D.dtype != torch.float32 or means3D.device != self.device):
+            raise ValueError("factored collective needs means3D: the contiguous float32 [P,3] positions on this device")
+        self._factors_fresh = False
         if grads is not None:
             stray = {k: g for k, g in grads.items() if g is not None and k in views
                      and g.data_ptr() != views[k].data_ptr()}
             if stray:
                 for k, g in stray.items():
-                    views[k].copy_(g.reshape(views[k].shape))
+                    if not (use_factored and k == "shs"):          # factored: the rows are rebuilt, not reduced
+                        views[k].copy_(g.reshape(views[k].shape))
                 self._copy_back = (stray, views)
         a = self._libmod.PeerReduceArgs()
         off = self.flag_bytes + self._cur * self.slot_bytes
-        if radii is not None and self.sh_coeffs == 16 and not self.multimem and self._copy_back is None:
+        if (radii is not None and self.sh_coeffs == 16 and not self.multimem and self._copy_back is None
+                and not use_factored):
             if radii.dtype != torch.int32 or radii.numel() != self.P or not radii.is_cuda or not radii.is_contiguous():
                 raise ValueError("radii must be a contiguous int32 CUDA tensor with one entry per Gaussian")
             a.radii = radii.data_ptr()
@@ -314,7 +422,9 @@ class PeerGradientAllReduce:
             a.peer_bufs[r] = self.mem.ptrs[r] + off
             a.peer_flags[r] = self.mem.ptrs[r]
         a.multicast_buf = (self.mem.multicast_ptr + off) if self.multimem else None
-        a.n_floats = self.n_floats
+        a.n_floats = self.dense_floats if use_factored else self.n_floats
+        if use_factored:
+            a.gather_offset_floats, a.gather_floats = self.n_floats, self.slot_floats
         a.rank, a.world = self.rank, self.world
         self._epoch += 1
         a.epoch = self._epoch
@@ -325,6 +435,17 @@ class PeerGradientAllReduce:
         self._stream.wait_event(ready)
         self._libmod.check(self._lib.b200s_peer_allreduce_sum_f32(a, self._stream.cuda_stream),
                            "b200s_peer_allreduce_sum_f32")
+        if use_factored:
+            import ctypes as C
+            sg = self._libmod.ShGradArgs()
+            sg.P, sg.D, sg.M, sg.views = self.P, int(sh_degree), self.sh_coeffs, self.world
+            sg.means3D = means3D.data_ptr()
+            sg.factors = self._flat[self._cur].data_ptr() + 4 * self.n_floats
+            sg.stride_floats = self.slot_floats
+            sg.dL_dsh = views["shs"].data_ptr()
+            self._means_keep = means3D
+            self._libmod.check(self._lib.b200s_sh_grad_reconstruct(C.byref(sg), self._stream.cuda_stream),
+                               "b200s_sh_grad_reconstruct")
         self._done = torch.cuda.Event()
         self._done.record(self._stream)
 

@@ -98,7 +98,10 @@ class ViewParallelTrainer:
             else:
                 parallel.accumulate_(total, grads)
         if self.reducer is not None:
-            self.reducer.start(total)
+            if peer:
+                self.reducer.start(total, means3D=self.opt.activated["means3D"], sh_degree=self.sh_degree)
+            else:
+                self.reducer.start(total)
             self.reducer.wait()
         self.opt.step(total)
         return loss3

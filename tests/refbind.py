@@ -118,12 +118,22 @@ class RefDGR:
 
     def backward(self, *, bg, means3D, radii, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, dL_dpix,
                  shs=None, colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None,
-                 scale_modifier=1.0, debug=False, sync=True):
+                 scale_modifier=1.0, debug=False, sync=True, out=None):
+        """`out`: optional {name: preallocated tensor} (e.g. views of one flat buffer for a single-call all-reduce);
+        those are zero-filled in place instead of allocated with torch.zeros (same memset bytes as the binding)."""
         dev = means3D.device
         P, M = self.P, self.M
-        z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)  # noqa: E731
-        g = dict(means2D=z(P, 3), conic=z(P, 2, 2), opacity=z(P, 1), colors=z(P, 3), means3D=z(P, 3),
-                 cov3D=z(P, 6), sh=z(P, M, 3), scales=z(P, 3), rotations=z(P, 4))
+
+        def z(name, *s):
+            t = out.get(name) if out else None
+            if t is None:
+                return torch.zeros(*s, dtype=torch.float32, device=dev)
+            assert t.numel() == int(np.prod(s)) and t.dtype == torch.float32 and t.is_contiguous()
+            return t.zero_().view(*s)
+
+        g = dict(means2D=z("means2D", P, 3), conic=z("conic", P, 2, 2), opacity=z("opacity", P, 1),
+                 colors=z("colors", P, 3), means3D=z("means3D", P, 3), cov3D=z("cov3D", P, 6), sh=z("sh", P, M, 3),
+                 scales=z("scales", P, 3), rotations=z("rotations", P, 4))
         if sync:
             torch.cuda.synchronize(dev)
         rc = self.lib.ref_dgr_backward(self.h, P, self.D, M, self.R, _p(bg), self.W, self.H, _p(means3D), _p(shs),

@@ -115,6 +115,19 @@ def _worker(rank, world, port, q):
         st.add_view(torch.ones(P, 3), vis)
         st.allreduce()
         ok = ok and float(st.denom.sum()) == P and abs(float(st.accum.sum()) - P * 2 ** 0.5) < 1e-3
+        # single-call flat-buffer all-reduce: gradients written into views of the flat buffer (no copy), strays copied
+        flat = par.FlatGradientAllReduce(P, 16, "cpu")
+        for step in range(3):                     # buffers rotate
+            views_ = flat.grad_out()
+            for k, t in views_.items():
+                t.fill_(float(rank + 1) * (step + 1))
+            stray = torch.full((P, 3), float(rank + 1))
+            flat.start({**views_, "scales": stray})
+            flat.wait()
+            want = sum(r + 1 for r in range(world)) * (step + 1)
+            ok = ok and all(float(t.min()) == want and float(t.max()) == want
+                            for k, t in views_.items() if k != "scales")
+            ok = ok and float(stray.min()) == sum(r + 1 for r in range(world))
         params["means3D"][0, 0] += float(rank)    # deliberately diverge -> must be detected
         ok = ok and not par.replicas_in_sync(params.values())
         q.put((rank, ok))
@@ -134,3 +147,46 @@ def test_gradient_allreduce_world2_gloo():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert sorted(res) == [(0, True), (1, True)]
+
+
+def test_sh_gradient_of_a_view_is_rank_one():
+    """The identity the factored collective rests on (csrc/sh_reconstruct.cu): for one view,
+    d(colour . w)/d sh[k][c] = basis_k(dir) * w[c], so 3 floats per Gaussian and view determine the 48-float row and
+    the sum over views can be rebuilt from the gathered factors. Checked with autograd through the reference's own
+    eval_sh polynomial (utils/sh_utils.py:57-112 as restated in sh_utils.py)."""
+    from neuralgaussiansplatting_b200.sh_utils import eval_sh
+    g = torch.Generator().manual_seed(5)
+    P, V = 64, 3
+    means = torch.randn(P, 3, generator=g, dtype=torch.float64)
+    total_dense = torch.zeros(P, 16, 3, dtype=torch.float64)
+    total_fact = torch.zeros(P, 16, 3, dtype=torch.float64)
+    for v in range(V):
+        campos = torch.randn(3, generator=g, dtype=torch.float64) * 4
+        w = torch.randn(P, 3, generator=g, dtype=torch.float64)
+        d = means - campos
+        d = d / d.norm(dim=1, keepdim=True)
+        sh = torch.randn(P, 16, 3, generator=g, dtype=torch.float64, requires_grad=True)
+        col = eval_sh(3, sh.transpose(1, 2), d)
+        (col * w).sum().backward()
+        total_dense += sh.grad
+        # basis_k(dir) = d colour_c / d sh[k][c] for any c: read it off with a one-hot coefficient tensor
+        eye = torch.eye(16, dtype=torch.float64)[None, :, :, None].expand(P, 16, 16, 1)    # [P, k, coeff, 1]
+        basis = torch.stack([eval_sh(3, eye[:, k].expand(P, 16, 3).transpose(1, 2), d)[:, 0] for k in range(16)], dim=1)
+        total_fact += basis[:, :, None] * w[:, None, :]
+    assert torch.allclose(total_dense, total_fact, atol=1e-12)
+
+
+def test_factored_layout_of_the_peer_buffer():
+    """Gather slots sit behind the five tensors, 256-byte aligned, one per rank, each holding 3P factors + the camera
+    centre; the dense prefix the collective sums is everything before dL/dsh."""
+    for P in (1, 257, 10_007, 3_000_000):
+        lay, total = par.gradient_layout(P, 16)
+        slot = -(-(3 * P + 4) // 64) * 64
+        assert slot % 64 == 0 and slot >= 3 * P + 4
+        assert lay["shs"][0] % 64 == 0 and lay["shs"][0] >= 11 * P
+        assert lay["shs"][0] + 48 * P <= total
+    # NVLink bytes per GPU and direction at the bench size, world 8: dense two-shot vs factored
+    P, W = 3_000_000, 8
+    dense = 2 * (W - 1) / W * 236 * P
+    fact = 2 * (W - 1) / W * 44 * P + (W - 1) * 12 * P
+    assert dense / fact > 2.5
