@@ -840,7 +840,9 @@ def render_only(args, rank, world, dev, impl):
 
     img_host = [torch.empty(3, cfg.height, cfg.width).pin_memory() for _ in range(2)]
     img_ev = [None, None]
+    img_keep = [None, None]
     cam_dev = [torch.empty(35, device=dev) for _ in range(2)]
+    copy_stream = torch.cuda.Stream(device=dev)
     cnt = {"n": 0}
 
     def e2e_pass(_s):
@@ -850,12 +852,20 @@ def render_only(args, rank, world, dev, impl):
             cd = cam_dev[i]
             cd.copy_(cam_host[v], non_blocking=True)
             img = render(cd[0:16].view(4, 4), cd[16:32].view(4, 4), cd[32:35])
+            rendered = torch.cuda.Event()
+            rendered.record(torch.cuda.current_stream(dev))
             if img_ev[i] is not None:
                 img_ev[i].synchronize()          # the host consumed (here: may overwrite) this pinned buffer
-            img_host[i].copy_(img, non_blocking=True)
-            ev = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream(dev))
-            img_ev[i] = ev
+            with torch.cuda.stream(copy_stream):     # image k goes to the host while view k+1 is rasterized
+                copy_stream.wait_event(rendered)
+                img_host[i].copy_(img, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+            img.record_stream(copy_stream)
+            img_ev[i], img_keep[i] = ev, img
+        for ev in img_ev:                        # every image of the pass is on the host before the region ends
+            if ev is not None:
+                torch.cuda.current_stream(dev).wait_event(ev)
 
     for v in mine[:max(3, min(len(mine), 8))]:                    # warm-up (also sizes the binning workspaces)
         c = cams[v]
@@ -875,7 +885,8 @@ def render_only(args, rank, world, dev, impl):
             "e2e": {"value": round(total / (ms_e2e * 1e-3), 2), "unit": "views/s",
                     "ms_per_view_per_gpu": round(ms_e2e / max(len(mine) * passes, 1), 4),
                     "h2d_bytes_per_view": 35 * 4, "d2h_bytes_per_view": 3 * cfg.height * cfg.width * 4,
-                    "what": "camera block H2D + rendered image D2H to pinned host memory per view, double-buffered; "
+                    "what": "camera block H2D + rendered image D2H to pinned host memory per view on a copy stream (image k "
+                            "leaves while view k+1 is rasterized), double-buffered; "
                             "no gather to rank 0 (every rank keeps / writes its own views, as render.py does per view)"},
             "impl": impl}
 

@@ -218,3 +218,5 @@ def test_peer_allreduce_two_ranks_exact():
     assert r.returncode == 0, r.stderr[-2000:]
     rep = json.loads(r.stdout.strip().splitlines()[-1])
     assert rep["stray_copy_path"] and all(rep[f"small_trial{i}"]["exact_fixed_order_sum"] for i in range(3))
+    assert all(rep[f"factored_trial{i}"]["exact_fixed_order_sum"] and rep[f"factored_trial{i}"]["replicas_identical"]
+               for i in range(3))

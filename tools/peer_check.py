@@ -30,7 +30,7 @@ def main():
     report = {"world": world}
 
     # ---- exactness on a small problem (all_gather of the inputs is affordable)
-    small = parallel.PeerGradientAllReduce(10_007, 16, dev, ctas=4, backend=a.backend)
+    small = parallel.PeerGradientAllReduce(10_007, 16, dev, ctas=4, backend=a.backend, factored=False)
     report["backend"] = small.mem.backend
     report["multicast"] = bool(small.mem.multicast_ptr)
     for trial in range(3):
@@ -86,6 +86,55 @@ def main():
     assert all(bool((v == tot).all()) for v in stray.values())
     report["stray_copy_path"] = True
     del small
+    # ---- factored SH gradient: 11 dense floats summed, 3-float factors gathered, dL/dsh rebuilt locally. Expected
+    # rows: each rank's own dense row block (b200s_sh_grad_reconstruct on ITS slot alone == what b200s_backward writes,
+    # tests/test_factored_sh_gpu.py), all-gathered and summed in rank order with torch.
+    import ctypes as C
+    from neuralgaussiansplatting_b200 import _lib
+    lib = _lib.load()
+    Pf = 10_007
+    fact = parallel.PeerGradientAllReduce(Pf, 16, dev, ctas=4, backend=a.backend, factored=True)
+    gm = torch.Generator(device=dev).manual_seed(4242)                 # replicated positions: same seed everywhere
+    means = torch.randn(Pf, 3, device=dev, generator=gm) * 2.0
+    for trial in range(3):
+        views = fact.grad_out()
+        g = torch.Generator(device=dev).manual_seed(5000 + 100 * trial + rank)
+        for k, v in views.items():
+            if k not in ("shs", "sh_factors"):
+                v.copy_(torch.randn(v.shape, device=dev, generator=g))
+        views["shs"].fill_(float("nan"))                                   # must be fully overwritten
+        slot = views["sh_factors"]
+        rgb = torch.randn(Pf, 3, device=dev, generator=g)
+        rgb[torch.rand(Pf, device=dev, generator=g) < 0.57] = 0.0          # culled in this rank's view
+        slot[:3 * Pf].copy_(rgb.reshape(-1))
+        slot[3 * Pf:3 * Pf + 3].copy_(torch.randn(3, device=dev, generator=g) * 4.0)
+        own_rows = torch.empty(Pf, 16, 3, device=dev)
+        sg = _lib.ShGradArgs()
+        sg.P, sg.D, sg.M, sg.views = Pf, 3, 16, 1
+        sg.means3D, sg.factors, sg.stride_floats, sg.dL_dsh = means.data_ptr(), slot.data_ptr(), fact.slot_floats, own_rows.data_ptr()
+        _lib.check(lib.b200s_sh_grad_reconstruct(C.byref(sg), torch.cuda.current_stream().cuda_stream), "reconstruct")
+        expect = {}
+        for k, v in list(views.items()) + [("shs_rows", own_rows)]:
+            if k in ("shs", "sh_factors"):
+                continue
+            parts = [torch.empty_like(v) for _ in range(world)]
+            dist.all_gather(parts, v.clone())
+            e = parts[0].clone()
+            for q in parts[1:]:
+                e += q
+            expect[k] = e
+        fact.start(views, means3D=means, sh_degree=3)
+        fact.wait()
+        torch.cuda.synchronize()
+        exact = all(bool(torch.equal(views[k], expect[k])) for k in expect if k != "shs_rows")
+        exact = exact and bool(torch.equal(views["shs"], expect["shs_rows"]))
+        chk = torch.stack([views[k].double().sum() for k in ("means3D", "opacities", "scales", "rotations", "shs")])
+        allc = [torch.empty_like(chk) for _ in range(world)]
+        dist.all_gather(allc, chk)
+        same = all(torch.equal(allc[0], x) for x in allc[1:])
+        report[f"factored_trial{trial}"] = {"exact_fixed_order_sum": exact, "replicas_identical": same}
+        assert exact and same, report
+    del fact
     if a.quick:
         if rank == 0:
             print(json.dumps(report))
@@ -111,10 +160,11 @@ def main():
     times = {}
     g = torch.Generator(device=dev).manual_seed(7 + rank)
     radii43 = (torch.rand(a.P, device=dev, generator=g) < 0.43).to(torch.int32)
-    for mm in (False, "sparse", True):
-        for ctas in (8, 16, 32):
+    means_big = torch.randn(a.P, 3, device=dev, generator=torch.Generator(device=dev).manual_seed(1))
+    for mm, fct in ((False, True), (True, True), (False, False), ("sparse", False), (True, False)):
+        for ctas in (4, 8, 16, 32):
             red = parallel.PeerGradientAllReduce(a.P, 16, dev, ctas=ctas, multimem=(mm is True), n_buffers=1,
-                                                 backend=a.backend)
+                                                 backend=a.backend, factored=fct)
             if mm is True and not red.multimem:
                 del red
                 break
@@ -124,11 +174,21 @@ def main():
                 rad = radii43
                 for v in views.values():
                     v[rad <= 0] = 0.0
+            if fct:
+                views["sh_factors"].zero_()
+                views["sh_factors"][:3 * a.P].copy_(torch.randn(3 * a.P, device=dev))
+                views["sh_factors"][:3 * a.P].view(a.P, 3)[radii43 <= 0] = 0.0     # 43 % of the rows visible per view
 
             def fn():
-                red.start(None, radii=rad); red.wait()
+                if fct:
+                    red._factors_fresh = True
+                    red.start(None, means3D=means_big, sh_degree=3)
+                else:
+                    red.start(None, radii=rad)
+                red.wait()
             ms = time_it(fn, a.iters)
-            times[f"{'multimem' if mm is True else 'sparse43' if mm else 'p2p'}_ctas{ctas}"] = {"ms": round(ms, 4), "algbw_GBps": round(nbytes / ms / 1e6, 1)}
+            name = ("factored_" if fct else "") + ("multimem" if mm is True else "sparse43" if mm else "p2p")
+            times[f"{name}_ctas{ctas}"] = {"ms": round(ms, 4), "algbw_GBps": round(nbytes / ms / 1e6, 1)}
             del red
             torch.cuda.empty_cache()
     x = torch.zeros(n_floats, device=dev)
