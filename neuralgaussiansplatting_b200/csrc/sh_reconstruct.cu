@@ -27,7 +27,7 @@ struct ShReconParams {
 };
 
 template <bool SH16>
-__global__ void __launch_bounds__(SR_THREADS)
+__global__ void __launch_bounds__(SR_THREADS, 4)
 sh_grad_reconstruct_kernel(const __grid_constant__ ShReconParams p) {
     __shared__ __align__(16) float tile[SR_THREADS * SH_ROW_PAD];
     __shared__ float s_cam[SR_MAX_VIEWS][4];
@@ -43,20 +43,32 @@ sh_grad_reconstruct_kernel(const __grid_constant__ ShReconParams p) {
     for (int i = 0; i < SH_ROW_FLOATS; ++i) acc[i] = 0.0f;
     if (in_range) {
         const float mx = p.means3D[3 * idx], my = p.means3D[3 * idx + 1], mz = p.means3D[3 * idx + 2];
-        for (int v = 0; v < p.views; ++v) {
-            const float* g = p.factors + (size_t)v * p.stride + 3 * idx;
-            const float gx = g[0], gy = g[1], gz = g[2];
-            if (gx == 0.0f && gy == 0.0f && gz == 0.0f) continue;     // culled / clamped in view v: an all-zero row
-            float3 dir_orig, dir;
-            sh_view_dir(mx, my, mz, s_cam[v][0], s_cam[v][1], s_cam[v][2], dir_orig, dir);
-            float bas[16];
-            sh_basis(p.D, dir.x, dir.y, dir.z, bas);
+        // the factor loads of eight views are issued back to back before any of them is consumed (the kernel is
+        // HBM-latency bound otherwise: one dependent 12-byte load per view and thread)
+        for (int v0 = 0; v0 < p.views; v0 += 8) {
+            float gx[8], gy[8], gz[8];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                if (k < ncoef) {
-                    acc[3 * k] = fadd(acc[3 * k], fmul(bas[k], gx));
-                    acc[3 * k + 1] = fadd(acc[3 * k + 1], fmul(bas[k], gy));
-                    acc[3 * k + 2] = fadd(acc[3 * k + 2], fmul(bas[k], gz));
+            for (int q = 0; q < 8; ++q) {
+                gx[q] = gy[q] = gz[q] = 0.0f;
+                if (v0 + q < p.views) {
+                    const float* g = p.factors + (size_t)(v0 + q) * p.stride + 3 * idx;
+                    gx[q] = __ldg(g); gy[q] = __ldg(g + 1); gz[q] = __ldg(g + 2);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                if (gx[q] == 0.0f && gy[q] == 0.0f && gz[q] == 0.0f) continue;   // culled / clamped in that view: an all-zero row
+                float3 dir_orig, dir;
+                sh_view_dir(mx, my, mz, s_cam[v0 + q][0], s_cam[v0 + q][1], s_cam[v0 + q][2], dir_orig, dir);
+                float bas[16];
+                sh_basis(p.D, dir.x, dir.y, dir.z, bas);
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    if (k < ncoef) {
+                        acc[3 * k] = fadd(acc[3 * k], fmul(bas[k], gx[q]));
+                        acc[3 * k + 1] = fadd(acc[3 * k + 1], fmul(bas[k], gy[q]));
+                        acc[3 * k + 2] = fadd(acc[3 * k + 2], fmul(bas[k], gz[q]));
+                    }
                 }
             }
         }
