@@ -175,7 +175,7 @@ def stage_table(w: Workload, stage_ms, stage_calls, steps, counts, P_vis, N, hbm
     passes = -(-(32 + max(T - 1, 1).bit_length()) // 8)
     n_trav, n_contrib, n_trav_bwd = counts
     alg = {
-        "preprocess": ("hbm", 311 * P_vis + 20 * P_c + 8 * P),     # K1 + K2: the scan is fused into the preprocess
+        "preprocess": ("hbm", 311 * P_vis + 20 * P_c),
         "scan": ("hbm", 8 * P),
         "expand": ("hbm", 20 * P + 12 * N),
         "sort": ("hbm", N * (8 + 24 * passes)),
@@ -189,6 +189,7 @@ def stage_table(w: Workload, stage_ms, stage_calls, steps, counts, P_vis, N, hbm
     # u32 tile keys + u32 ids through `tile_passes` onesweep passes and presorts the visible set on depth.
     tile_passes = -(-max(T - 1, 1).bit_length() // 8)
     moved = {
+        "scan": 4 * P + 8 * P_vis,
         "expand": 4 * 16 * P_vis + 8 * N,
         "sort": 16 * N * tile_passes + 4 * N,
         "ranges": 4 * N + 8 * T,
@@ -924,11 +925,6 @@ def main():
         raise SystemExit(f"--gpus {args.gpus} needs torchrun (WORLD_SIZE={world})")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    # stdout carries exactly ONE JSON line: everything libraries print there while the run is in flight (NCCL's
-    # version banner, ...) is sent to stderr; the saved descriptor is used for the final line only
-    sys.stdout.flush()
-    json_fd = os.dup(1)
-    os.dup2(2, 1)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # stdout carries exactly one JSON line
@@ -938,8 +934,7 @@ def main():
         res = run_reference(args, rank, local_rank, world, dev) if args.impl == "reference" else \
             run_ours(args, rank, local_rank, world, dev)
         if rank == 0:
-            sys.stdout.flush()
-            os.write(json_fd, (json.dumps(res) + "\n").encode())
+            print(json.dumps(res), flush=True)
     finally:
         if world > 1:
             dist.barrier()

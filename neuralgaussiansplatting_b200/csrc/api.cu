@@ -49,23 +49,6 @@ void prof_end(int stage, cudaStream_t stream) {
 }
 }  // namespace b200s
 
-namespace b200s {
-// Zero the raw-sum rows of the visible Gaussians only: the count is on the device, so the grid is sized for
-// P and the blocks beyond num_visible exit after one header read.
-__global__ void __launch_bounds__(256)
-zero_accum_kernel(float4* accum, const B200sHeader* header) {
-    const size_t n4 = (size_t)header->num_visible * (ACC_STRIDE / 4);
-    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-    if (i < n4) accum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-}
-int launch_zero_accum(float* accum, const B200sHeader* header, int64_t P, cudaStream_t stream) {
-    const size_t n4 = (size_t)P * (ACC_STRIDE / 4);
-    count_launch();
-    zero_accum_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, stream>>>(reinterpret_cast<float4*>(accum), header);
-    return (int)cudaGetLastError();
-}
-}  // namespace b200s
-
 extern "C" int b200s_profile_begin(void) {
     std::lock_guard<std::mutex> lk(g_prof_mu);
     for (auto& b : g_brackets) { cudaEventDestroy(b.e0); cudaEventDestroy(b.e1); }
@@ -211,9 +194,8 @@ int b200s_forward_preprocess(const B200sForwardArgs* a, b200s_stream_t stream_) 
     p.means3D = a->means3D; p.shs = a->shs; p.colors_precomp = a->colors_precomp; p.opacities = a->opacities;
     p.scales = a->scales; p.rotations = a->rotations; p.cov3D_precomp = a->cov3D_precomp;
     p.viewmatrix = a->viewmatrix; p.projmatrix = a->projmatrix; p.campos = a->campos;
-    p.radii = a->radii; p.rec = g.rec; p.tiles_touched = g.tiles_touched; p.point_offsets = g.point_offsets;
-    p.clamped = g.clamped; p.rank_to_id = g.rank_to_id; p.vis_offsets = g.vis_offsets; p.block_base = g.block_base;
-    p.vis_keys = g.vis_keys[0]; p.vis_ranks = g.vis_ids[0]; p.scan_status = g.scan_status;
+    p.radii = a->radii; p.rec = g.rec; p.tiles_touched = g.tiles_touched; p.depth_bits = g.depth_bits;
+    p.clamped = g.clamped;
     p.header = g.header; p.counters = g.counters;
     {
         ProfScope ps(B200S_STAGE_PREPROCESS, stream);
@@ -221,7 +203,7 @@ int b200s_forward_preprocess(const B200sForwardArgs* a, b200s_stream_t stream_) 
     }
     if (rc) return rc;
     B200S_AFTER_LAUNCH(stream, a->debug);
-    return launch_depth_sort(a->P, g, a->debug != 0, stream);
+    return launch_scan_and_depth_sort(a->P, g, a->debug != 0, stream);
 }
 
 int b200s_forward_render(const B200sForwardArgs* a, b200s_stream_t stream_) {
@@ -312,16 +294,14 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
         if (a->deterministic) {
             B200S_CUDA_OK(cudaMemsetAsync(ws.partial, 0, sizeof(float) * ACC_STRIDE * (size_t)(a->num_rendered > 0 ? a->num_rendered : 1), stream));
         } else {
-            // only the rows of the visible Gaussians (the count lives in the device header)
-            const int rcz = launch_zero_accum(ws.accum, g.header, a->P, stream);
-            if (rcz) return rcz;
+            B200S_CUDA_OK(cudaMemsetAsync(ws.accum, 0, sizeof(float) * ACC_STRIDE * (size_t)a->P, stream));
         }
     }
     if (a->num_rendered > 0) {
         BlendBwdParams b;
         b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;
         b.ranges = im.ranges; b.point_list = bw.vals[final_buf]; b.rec = g.rec;
-        b.vis_offsets = g.vis_offsets;
+        b.point_offsets = g.point_offsets;
         b.background = a->background; b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last;
         b.dL_dpix = a->dL_dout_color; b.accum = ws.accum; b.partial = ws.partial; b.deterministic = a->deterministic;
         int rc;
@@ -339,7 +319,7 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
     p.means3D = a->means3D; p.shs = a->shs; p.colors_precomp = a->colors_precomp; p.scales = a->scales;
     p.rotations = a->rotations; p.cov3D_precomp = a->cov3D_precomp; p.viewmatrix = a->viewmatrix;
     p.projmatrix = a->projmatrix; p.campos = a->campos; p.radii = a->radii; p.rec = g.rec; p.clamped = g.clamped;
-    p.point_offsets = g.point_offsets; p.block_base = g.block_base;
+    p.point_offsets = g.point_offsets;
     p.accum = a->deterministic ? nullptr : ws.accum;
     p.partial = a->deterministic ? ws.partial : nullptr;
     p.dL_dmeans3D = a->dL_dmeans3D; p.dL_dmeans2D = a->dL_dmeans2D; p.dL_dopacity = a->dL_dopacity;
@@ -468,24 +448,14 @@ extern "C" int b200s_count_pairs(const B200sForwardArgs* a, unsigned long long* 
 
 // ---------------------------------------------------------------------------- state export
 namespace {
-// Records live by visible rank: thread i recomputes the rank of Gaussian i from its block's base + the
-// number of visible Gaussians before it in the block (blockDim.x == PRE_BLOCK).
-__global__ void __launch_bounds__(PRE_BLOCK)
-export_rec_kernel(int P, const SplatRec* rec, const int* radii, const uint8_t* clamped, const uint32_t* block_base,
-                  int which, float* dst_f, uint8_t* dst_b) {
-    __shared__ uint32_t s_w[PRE_BLOCK / 32];
-    const int64_t i = (int64_t)blockIdx.x * PRE_BLOCK + threadIdx.x;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const bool vis = i < P && radii[i] > 0;
-    const uint32_t m = __ballot_sync(FULL_MASK, vis);
-    if (lane == 0) s_w[warp] = __popc(m);
-    __syncthreads();
-    uint32_t rank = block_base[blockIdx.x] + __popc(m & lanemask_lt());
-    for (int w = 0; w < warp; ++w) rank += s_w[w];
+__global__ void export_rec_kernel(int P, const SplatRec* rec, const int* radii, const uint8_t* clamped, int which,
+                                  float* dst_f, uint8_t* dst_b) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P) return;
+    const bool vis = radii[i] > 0;
     SplatRec r;
     r.q0 = r.q1 = r.q2 = make_float4(0, 0, 0, 0);
-    if (vis) r = rec[rank];
+    if (vis) r = rec[i];
     switch (which) {
         case B200S_STATE_DEPTHS: dst_f[i] = r.q2.y; break;
         case B200S_STATE_MEANS2D: dst_f[2 * i] = r.q0.x; dst_f[2 * i + 1] = r.q0.y; break;
@@ -493,15 +463,10 @@ export_rec_kernel(int P, const SplatRec* rec, const int* radii, const uint8_t* c
             dst_f[4 * i] = r.q0.z; dst_f[4 * i + 1] = r.q0.w; dst_f[4 * i + 2] = r.q1.x; dst_f[4 * i + 3] = r.q1.y; break;
         case B200S_STATE_RGB: dst_f[3 * i] = r.q1.z; dst_f[3 * i + 1] = r.q1.w; dst_f[3 * i + 2] = r.q2.x; break;
         case B200S_STATE_CLAMPED: {
-            const uint8_t c = vis ? clamped[rank] : 0;
+            const uint8_t c = vis ? clamped[i] : 0;
             dst_b[3 * i] = c & 1; dst_b[3 * i + 1] = (c >> 1) & 1; dst_b[3 * i + 2] = (c >> 2) & 1; break;
         }
     }
-}
-// point_list holds visible ranks internally: translate to Gaussian ids
-__global__ void export_ids_kernel(int64_t n, const uint32_t* ranks, const uint32_t* rank_to_id, uint32_t* dst) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) dst[i] = rank_to_id[ranks[i]];
 }
 // The sorted 64-bit keys are not materialised by the two-level sort (the blend only needs the
 // sorted Gaussian ids): rebuild them as tile << 32 | depth bits of the sorted ids.
@@ -542,16 +507,8 @@ extern "C" int64_t b200s_export_state(const B200sForwardArgs* a, int32_t which, 
             if (!a->bin_ws || num_rendered > a->bin_capacity) return B200S_E_BADARG;
             BinWS bw = carve_bin(a->bin_ws, a->bin_capacity);
             const int fb = sort_num_passes(d.tiles) & 1;
-            if (which == B200S_STATE_POINT_LIST) {
-                bytes = 4 * num_rendered;
-                if (bytes > dst_bytes) return B200S_E_WORKSPACE;
-                if (bytes == 0) return 0;
-                count_launch();
-                export_ids_kernel<<<(unsigned)((num_rendered + 255) / 256), 256, 0, stream>>>(
-                    num_rendered, bw.vals[fb], g.rank_to_id, (uint32_t*)dst);
-                if (cudaGetLastError() != cudaSuccess) return B200S_E_BADARG;
-                return bytes;
-            } else {
+            if (which == B200S_STATE_POINT_LIST) { src = bw.vals[fb]; bytes = 4 * num_rendered; }
+            else {
                 bytes = 8 * num_rendered;
                 if (bytes > dst_bytes) return B200S_E_WORKSPACE;
                 if (bytes == 0) return 0;
@@ -571,8 +528,8 @@ extern "C" int64_t b200s_export_state(const B200sForwardArgs* a, int32_t which, 
         if (cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, stream) != cudaSuccess) return B200S_E_BADARG;
     } else {
         count_launch();
-        export_rec_kernel<<<(unsigned)((P + PRE_BLOCK - 1) / PRE_BLOCK), PRE_BLOCK, 0, stream>>>(
-            (int)P, g.rec, a->radii, g.clamped, g.block_base, which, (float*)dst, (uint8_t*)dst);
+        export_rec_kernel<<<(unsigned)((P + 255) / 256), 256, 0, stream>>>((int)P, g.rec, a->radii, g.clamped, which,
+                                                                         (float*)dst, (uint8_t*)dst);
         if (cudaGetLastError() != cudaSuccess) return B200S_E_BADARG;
     }
     return bytes;

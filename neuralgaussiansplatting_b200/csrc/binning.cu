@@ -30,9 +30,92 @@
 
 #include <cstdlib>
 #include "kernels.cuh"
-#include "lookback.cuh"
 
 namespace b200s {
+
+constexpr uint32_t FLAG_AGG = 1u, FLAG_INCL = 2u;
+constexpr int SPIN_LIMIT = 1 << 22;
+
+// Spins until the look-back word at `p` carries a flag; returns the word. A bounded spin:
+// on timeout raises ERR_LOOKBACK_TIMEOUT and returns an "inclusive 0" word so that the
+// grid always terminates.
+__device__ __forceinline__ uint32_t wait_status(const uint32_t* p, B200sHeader* header) {
+    uint32_t v = ld_volatile_u32(p);
+    int spins = 0;
+    while ((v & 3u) == 0u) {
+        if (++spins > SPIN_LIMIT) {
+            atomicOr(&header->error, (uint32_t)ERR_LOOKBACK_TIMEOUT);
+            return FLAG_INCL;
+        }
+        __nanosleep(20);
+        v = ld_volatile_u32(p);
+    }
+    return v;
+}
+
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long wait_status64(const unsigned long long* p, B200sHeader* header) {
+    unsigned long long v = ld_volatile_u64(p);
+    int spins = 0;
+    while ((v & 3ull) == 0ull) {
+        if (++spins > SPIN_LIMIT) {
+            atomicOr(&header->error, (uint32_t)ERR_LOOKBACK_TIMEOUT);
+            return (unsigned long long)FLAG_INCL;
+        }
+        __nanosleep(20);
+        v = ld_volatile_u64(p);
+    }
+    return v;
+}
+
+
+// Warp-cooperative decoupled look-back for a scan with ONE value per tile: the 32 lanes read the
+// 32 predecessors' status words at once and consume them up to the first inclusive word / first
+// word not yet published. Returns the exclusive prefix of `tile` (same value in every lane).
+// Packed u64 words (two fields) are summed as they are: the caller guarantees no carry between fields.
+template <typename T>
+__device__ __forceinline__ T warp_lookback(const T* status, int64_t tile, B200sHeader* header) {
+    const int lane = threadIdx.x & 31;
+    T excl = 0;
+    int64_t t = tile - 1;
+    int spins = 0;
+    while (t >= 0) {
+        const int64_t idx = t - lane;
+        T w = (T)FLAG_INCL;                       // virtual inclusive zero in front of tile 0
+        if (idx >= 0) {
+            if (sizeof(T) == 8) w = (T)ld_volatile_u64(reinterpret_cast<const unsigned long long*>(status + idx));
+            else w = (T)ld_volatile_u32(reinterpret_cast<const uint32_t*>(status + idx));
+        }
+        const uint32_t flag = (uint32_t)(w & (T)3);
+        const uint32_t nr = __ballot_sync(FULL_MASK, flag == 0u);
+        const uint32_t inc = __ballot_sync(FULL_MASK, flag == FLAG_INCL);
+        const int first_nr = nr ? __ffs(nr) - 1 : 32;
+        const int first_inc = inc ? __ffs(inc) - 1 : 32;
+        const bool done = first_inc < first_nr;
+        const int take = done ? first_inc + 1 : first_nr;
+        T v = lane < take ? (w >> 2) : (T)0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL_MASK, v, o);
+        excl += v;
+        if (done) break;
+        t -= take;
+        if (take == 0) {
+            if (++spins > SPIN_LIMIT) {
+                if (lane == 0) atomicOr(&header->error, (uint32_t)ERR_LOOKBACK_TIMEOUT);
+                break;
+            }
+            __nanosleep(20);
+        }
+    }
+    return excl;
+}
 
 // Per-thread look-back (one chain per radix digit) with LB independent loads in flight per step.
 #ifndef B200S_LB_DEPTH
@@ -66,6 +149,102 @@ __device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t 
         }
     }
     return excl;
+}
+
+// ---------------------------------------------------------------------- scan + compaction
+// Look-back word: bits [0,2) flag, [2,32) sum of tiles_touched, [32,64) number of visible.
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_compact_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict__ depth_bits,
+                    uint32_t* __restrict__ out, uint32_t* __restrict__ vis_keys, uint32_t* __restrict__ vis_ids,
+                    int P, unsigned long long* status, uint32_t* counters, B200sHeader* header) {
+    __shared__ uint32_t s_tile;
+    __shared__ unsigned long long s_prefix;
+    __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(&counters[CTR_SCAN_TICKET], 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const int64_t base = (int64_t)tile * SCAN_TILE + (int64_t)tid * SCAN_ITEMS;
+
+    uint32_t v[SCAN_ITEMS], dep[SCAN_ITEMS];
+    if (base + SCAN_ITEMS <= P) {
+        const uint4* src = reinterpret_cast<const uint4*>(in + base);
+        const uint4* dsrc = reinterpret_cast<const uint4*>(depth_bits + base);
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS / 4; ++i) {
+            const uint4 t = src[i];
+            v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+            const uint4 d = dsrc[i];
+            dep[4 * i] = d.x; dep[4 * i + 1] = d.y; dep[4 * i + 2] = d.z; dep[4 * i + 3] = d.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; ++i) {
+            v[i] = (base + i < P) ? in[base + i] : 0u;
+            dep[i] = (base + i < P) ? depth_bits[base + i] : 0u;
+        }
+    }
+    uint32_t tsum = 0, vmask = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+        if (v[i] != 0u) vmask |= 1u << i;
+        tsum += v[i]; v[i] = tsum;                     // thread-inclusive
+    }
+    const unsigned long long mine = (unsigned long long)tsum | ((unsigned long long)__popc(vmask) << 32);
+
+    unsigned long long incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long t = __shfl_up_sync(FULL_MASK, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    unsigned long long warp_excl = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < SCAN_THREADS / 32; ++w) {
+        const unsigned long long t = s_warp[w];
+        if (w < warp) warp_excl += t;
+        total += t;
+    }
+    if (warp == 0) {
+        // packed word << 2: the tile sum (< 2^32) moves to bits [2,34), the visible count (< 2^30,
+        // checked by the host) to [34,64)
+        if (lane == 0) st_volatile_u64(&status[tile], (total << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
+        unsigned long long excl = 0;
+        if (tile != 0) {
+            excl = warp_lookback<unsigned long long>(status, (int64_t)tile, header);
+            if (lane == 0) st_volatile_u64(&status[tile], ((excl + total) << 2) | FLAG_INCL);
+        }
+        if (lane == 0) s_prefix = excl;
+    }
+    __syncthreads();
+    const unsigned long long pre = s_prefix + warp_excl + (incl - mine);   // exclusive of this thread
+    const uint32_t off = (uint32_t)pre;
+    uint32_t ci = (uint32_t)(pre >> 32);
+    if (base + SCAN_ITEMS <= P) {
+        uint4* dst = reinterpret_cast<uint4*>(out + base);
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS / 4; ++i)
+            dst[i] = make_uint4(v[4 * i] + off, v[4 * i + 1] + off, v[4 * i + 2] + off, v[4 * i + 3] + off);
+    } else {
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; ++i)
+            if (base + i < P) out[base + i] = v[i] + off;
+    }
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+        if ((vmask >> i) & 1u) {
+            vis_keys[ci] = dep[i];
+            vis_ids[ci] = (uint32_t)(base + i);
+            ++ci;
+        }
+    }
+    // The thread that owns element P-1 publishes num_rendered and num_visible.
+    if (base <= (int64_t)P - 1 && (int64_t)P - 1 < base + SCAN_ITEMS) {
+        header->num_rendered = v[(P - 1) - base] + off;
+        header->num_visible = ci;
+    }
 }
 
 // ------------------------------------------------------------------------------- sort
@@ -465,11 +644,20 @@ static int set_sort_attr() {
     return 0;
 }
 
-// Stage 1b: depth sort of the visible Gaussians (the forward preprocess has already scanned tiles_touched and
-// compacted (depth bits, rank) in index order). Leaves the front-to-back ranks in g.vis_ids[0] (DEPTH_PASSES is even).
-int launch_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t stream) {
+// Stage 1b: point_offsets + num_rendered, compaction of the visible Gaussians, depth sort.
+// Leaves the front-to-back Gaussian ids in g.vis_ids[0] (DEPTH_PASSES is even).
+int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t stream) {
     if (P <= 0) return 0;
     { const int rc_attr = set_sort_attr(); if (rc_attr) return rc_attr; }
+    {
+        ProfScope ps(B200S_STAGE_SCAN, stream);
+        const int tiles = (P + SCAN_TILE - 1) / SCAN_TILE;
+        count_launch();
+        scan_compact_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(g.tiles_touched, g.depth_bits, g.point_offsets,
+                                                               g.vis_keys[0], g.vis_ids[0], P, g.scan_status,
+                                                               g.counters, g.header);
+        B200S_AFTER_LAUNCH(stream, debug);
+    }
     {
         ProfScope ps(B200S_STAGE_SORT, stream);
         const uint32_t* n_ptr = &g.header->num_visible;

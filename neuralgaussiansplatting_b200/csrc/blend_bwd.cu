@@ -178,7 +178,7 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
                 if (p.deterministic) {
                     // slot of this instance in the unsorted (Gaussian-major, tile-minor) order
                     const uint32_t rmin = __float_as_uint(q2.z), rwh = __float_as_uint(q2.w);
-                    const uint32_t first = idc[k] == 0 ? 0u : p.vis_offsets[idc[k] - 1];    // list values are visible ranks
+                    const uint32_t first = idc[k] == 0 ? 0u : p.point_offsets[idc[k] - 1];
                     dest = first + ((uint32_t)tile_y - (rmin >> 16)) * (rwh & 0xffffu) + ((uint32_t)tile_x - (rmin & 0xffffu));
                 }
                 q2.y = thr;

@@ -38,7 +38,9 @@ __host__ __device__ inline size_t align_up(size_t x, size_t a = WS_ALIGN) {
     return (x + a - 1) / a * a;
 }
 
-constexpr int PRE_BLOCK = 256;       // Gaussians per forward-preprocess block (= unit of the fused scan)
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 16;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
 // Radix sort geometry (see binning.cu).
 constexpr int SORT_RADIX_BITS = 8;
@@ -55,23 +57,17 @@ constexpr int EXP_ITEMS = 4;
 constexpr int EXP_TILE = EXP_THREADS * EXP_ITEMS;
 constexpr int EXP_OUT_TILE = EXP_THREADS * 8;   // instances emitted per expansion block
 
-// Everything the later stages gather per VISIBLE Gaussian is indexed by its visible rank (its position among the
-// visible Gaussians in index order, assigned by the scan fused into the forward preprocess), so the arrays are
-// dense: a view that sees 43 % of the scene touches 43 % of the sectors. Sort values and point_list hold RANKS
-// internally; rank_to_id turns them back into Gaussian ids for the parity export.
 struct GeomWS {
     B200sHeader* header;      // 64 B
     uint32_t* counters;       // 64 x u32 device tickets (scan ticket, sort tickets, ...)
-    SplatRec* rec;            // [P] by rank
-    uint32_t* tiles_touched;  // [P] by Gaussian id
-    uint32_t* point_offsets;  // [P] by id: inclusive prefix sum of tiles_touched (Gaussian-index order)
-    uint8_t* clamped;         // [P] by rank: bit c set when SH colour channel c was clamped at 0
-    uint32_t* rank_to_id;     // [P] by rank: Gaussian id
-    uint32_t* vis_offsets;    // [P] by rank: point_offsets of that Gaussian (deterministic backward slots)
-    uint32_t* block_base;     // [ceil(P / PRE_BLOCK) + 1] visible Gaussians before each preprocess block
-    uint32_t* vis_keys[2];    // [P] depth bits of the visible Gaussians in rank order (ping-pong)
-    uint32_t* vis_ids[2];     // [P] their ranks; after the depth sort: front-to-back order
-    unsigned long long* scan_status;   // [ceil(P / PRE_BLOCK) + 1] decoupled look-back words
+    SplatRec* rec;            // [P]
+    uint32_t* tiles_touched;  // [P]
+    uint32_t* point_offsets;  // [P] inclusive prefix sum of tiles_touched (Gaussian-index order)
+    uint8_t* clamped;         // [P] bit c set when SH colour channel c was clamped at 0
+    uint32_t* depth_bits;     // [P] view-space depth of visible Gaussians (float bits)
+    uint32_t* vis_keys[2];    // [P] depth bits of the compacted visible Gaussians (ping-pong)
+    uint32_t* vis_ids[2];     // [P] their Gaussian ids; after the depth sort: front-to-back order
+    unsigned long long* scan_status;   // [ceil(P / SCAN_TILE) + 1] decoupled look-back words
     uint32_t* depth_hist;     // [DEPTH_PASSES][SORT_RADIX]
     uint32_t* depth_lookback; // [DEPTH_PASSES][ceil(P / SORT_TILE)][SORT_RADIX]
     uint32_t* exp_status;     // [ceil(P / EXP_TILE) + 1] look-back words of the expansion
@@ -91,16 +87,14 @@ inline GeomWS carve_geom(void* base, int64_t P) {
     g.tiles_touched = (uint32_t*)take(4 * (size_t)P);
     g.point_offsets = (uint32_t*)take(4 * (size_t)P);
     g.clamped = (uint8_t*)take((size_t)P);
-    g.rank_to_id = (uint32_t*)take(4 * (size_t)P);
-    g.vis_offsets = (uint32_t*)take(4 * (size_t)P);
-    g.block_base = (uint32_t*)take(4 * ((size_t)(P + PRE_BLOCK - 1) / PRE_BLOCK + 1));
+    g.depth_bits = (uint32_t*)take(4 * (size_t)P);
     for (int i = 0; i < 2; ++i) {
         g.vis_keys[i] = (uint32_t*)take(4 * (size_t)P);
         g.vis_ids[i] = (uint32_t*)take(4 * (size_t)P);
     }
     g.depth_tiles = (P + SORT_TILE - 1) / SORT_TILE;
     g.zero_off = off;
-    g.scan_status = (unsigned long long*)take(8 * ((size_t)(P + PRE_BLOCK - 1) / PRE_BLOCK + 1));
+    g.scan_status = (unsigned long long*)take(8 * ((size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1));
     g.depth_hist = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * SORT_RADIX);
     g.depth_lookback = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * g.depth_tiles * SORT_RADIX);
     g.exp_status = (uint32_t*)take(4 * ((size_t)(P + EXP_TILE - 1) / EXP_TILE + 1));

@@ -22,14 +22,8 @@ struct PreprocessParams {
     int* radii;
     SplatRec* rec;
     uint32_t* tiles_touched;
-    uint32_t* point_offsets;
-    uint8_t* clamped;         // by rank
-    uint32_t* rank_to_id;     // by rank
-    uint32_t* vis_offsets;    // by rank
-    uint32_t* block_base;     // per preprocess block
-    uint32_t* vis_keys;       // by rank: depth bits
-    uint32_t* vis_ranks;      // by rank: identity (initial sort values)
-    unsigned long long* scan_status;
+    uint32_t* depth_bits;
+    uint8_t* clamped;
     B200sHeader* header;
     uint32_t* counters;
 };
@@ -51,7 +45,7 @@ struct BlendBwdParams {
     const uint2* ranges;
     const uint32_t* point_list;
     const SplatRec* rec;
-    const uint32_t* vis_offsets;     // by rank; deterministic mode: slot of an instance
+    const uint32_t* point_offsets;   // deterministic mode: slot of an instance
     const float* background;
     const float* final_T;
     const uint32_t* n_contrib;
@@ -76,8 +70,7 @@ struct PreprocessBwdParams {
     const float* campos;
     const int* radii;
     const SplatRec* rec;
-    const uint8_t* clamped;          // by rank
-    const uint32_t* block_base;      // visible Gaussians before each PRE_BLOCK-sized block (rank = base + prefix)
+    const uint8_t* clamped;
     const uint32_t* point_offsets;
     const float* accum;       // [P][ACC_STRIDE] (atomic mode) or NULL
     const float* partial;     // [R][ACC_STRIDE] (deterministic mode) or NULL
@@ -106,8 +99,7 @@ int launch_count_pairs(const BlendFwdParams& p, unsigned long long* counts, cuda
 
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
-int launch_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t stream);
-int launch_zero_accum(float* accum, const B200sHeader* header, int64_t P, cudaStream_t stream);
+int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t stream);
 int sort_num_passes(int tiles);
 int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, int64_t n_hint, int grid_x,
                    int tiles, uint2* ranges, int* final_buf, bool debug, cudaStream_t stream);

@@ -3,12 +3,6 @@
 // Replaces preprocessCUDA + helpers (reference forward.cu:20-256, auxiliary.h:41-164)
 // and checkFrustum (rasterizer_impl.cu:54-66).
 //
-// Fused with K2 (the reference's cub::DeviceScan::InclusiveSum over tiles_touched, rasterizer_impl.cu:277) and
-// with the compaction of the visible Gaussians: blocks take their 256 Gaussians in ticket order, publish
-// (sum of tiles_touched, number visible) as one packed word and look back over their predecessors (decoupled
-// look-back), so every visible Gaussian learns its slot offset AND its visible rank inside this kernel. Its
-// record, depth key, clamp bits and id are written BY RANK: everything the later stages gather is dense.
-//
 // One thread per Gaussian for the geometry chain (bit-exact, see common.cuh). The 192-B SH
 // rows — 62 % of the bytes this kernel reads — are not fetched by the owning thread with
 // strided scalar loads (the reference: 48 LDG.32 per thread, 32 lines per warp
@@ -17,12 +11,11 @@
 // then reads its own row conflict-free. Culled Gaussians cost 12 B read + 8 B written.
 
 #include "kernels.cuh"
-#include "lookback.cuh"
 
 namespace b200s {
 
 
-constexpr int PRE_THREADS = PRE_BLOCK;
+constexpr int PRE_THREADS = 256;
 constexpr int SH_ROW_FLOATS = 48;   // 16 coefficients x RGB
 constexpr int SH_ROW_PAD = 52;      // 208 B rows: 13 x 16 B => LDS.128 conflict-free
 constexpr size_t PRE_SMEM_SH16 = (size_t)PRE_THREADS * SH_ROW_PAD * sizeof(float);
@@ -87,66 +80,13 @@ __device__ __forceinline__ void cp_async_commit_wait_all() {
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
 
-// Block-wide inclusive scan of (tiles_touched, visible) + decoupled look-back over the preceding blocks.
-// Look-back word: bits [0,2) flag, [2,34) sum of tiles_touched (< 2^32), [34,64) number visible (< 2^30, checked
-// by the host). Returns this thread's inclusive tile offset and its exclusive visible count (= rank if visible).
-struct ScanResult { uint32_t offset_incl; uint32_t rank; };
-__device__ __forceinline__ ScanResult block_scan_lookback(const PreprocessParams& p, uint32_t tiles, bool visible,
-                                                          uint32_t vis_mask, uint32_t vblock,
-                                                          unsigned long long* s_warp, unsigned long long* s_prefix) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // warp-inclusive sum of tiles via shuffles; the visible count comes from the ballot
-    uint32_t incl = tiles;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(FULL_MASK, incl, o);
-        if (lane >= o) incl += t;
-    }
-    const uint32_t vis_before = __popc(vis_mask & lanemask_lt());
-    if (lane == 31) s_warp[warp] = (unsigned long long)incl | ((unsigned long long)__popc(vis_mask) << 32);
-    __syncthreads();
-    unsigned long long warp_excl = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < PRE_THREADS / 32; ++w) {
-        const unsigned long long t = s_warp[w];
-        if (w < warp) warp_excl += t;
-        total += t;
-    }
-    if (warp == 0) {
-        if (lane == 0) st_volatile_u64(&p.scan_status[vblock], (total << 2) | (vblock == 0 ? FLAG_INCL : FLAG_AGG));
-        unsigned long long excl = 0;
-        if (vblock != 0) {
-            excl = warp_lookback<unsigned long long>(p.scan_status, (int64_t)vblock, p.header);
-            if (lane == 0) st_volatile_u64(&p.scan_status[vblock], ((excl + total) << 2) | FLAG_INCL);
-        }
-        if (lane == 0) {
-            *s_prefix = excl;
-            p.block_base[vblock] = (uint32_t)(excl >> 32);
-        }
-    }
-    __syncthreads();
-    const unsigned long long pre = *s_prefix + warp_excl;
-    ScanResult r;
-    r.offset_incl = (uint32_t)pre + incl;
-    r.rank = (uint32_t)(pre >> 32) + vis_before;
-    (void)visible;
-    return r;
-}
-
 template <bool SH16>
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_fwd_kernel(const __grid_constant__ PreprocessParams p) {
     extern __shared__ __align__(16) float sh_tile[];   // [PRE_THREADS][SH_ROW_PAD] when SH16
-    __shared__ uint32_t s_block;
-    __shared__ unsigned long long s_prefix;
-    __shared__ unsigned long long s_warp[PRE_THREADS / 32];
     const int tid = threadIdx.x;
     const int lane = tid & 31;
-    // blocks are numbered in the order they START (ticket), so every predecessor in the look-back chain is running
-    if (tid == 0) s_block = atomicAdd(&p.counters[CTR_SCAN_TICKET], 1u);
-    __syncthreads();
-    const uint32_t vblock = s_block;
-    const int64_t idx = (int64_t)vblock * PRE_THREADS + tid;
+    const int64_t idx = (int64_t)blockIdx.x * PRE_THREADS + tid;
     const bool in_range = idx < p.P;
 
     bool visible = false;
@@ -207,8 +147,6 @@ preprocess_fwd_kernel(const __grid_constant__ PreprocessParams p) {
 
     float3 rgb = make_float3(0.f, 0.f, 0.f);
     uint32_t clamp_bits = 0;
-    ScanResult scan;
-    bool scanned = false;
     if (p.colors_precomp != nullptr) {
         if (visible) {
             rgb.x = p.colors_precomp[3 * idx + 0];
@@ -228,7 +166,7 @@ preprocess_fwd_kernel(const __grid_constant__ PreprocessParams p) {
             // Stream the visible rows of this warp's 32 Gaussians: 384 16-B chunks.
             const int warp = tid >> 5;
             float* tile = sh_tile + (size_t)warp * 32 * SH_ROW_PAD;
-            const float* gsrc = p.shs + ((int64_t)vblock * PRE_THREADS + warp * 32) * SH_ROW_FLOATS;
+            const float* gsrc = p.shs + ((int64_t)blockIdx.x * PRE_THREADS + warp * 32) * SH_ROW_FLOATS;
             if (vis_mask != 0) {
 #pragma unroll
                 for (int it = 0; it < 12; ++it) {
@@ -238,12 +176,8 @@ preprocess_fwd_kernel(const __grid_constant__ PreprocessParams p) {
                     if ((vis_mask >> row) & 1u)
                         cp_async16(tile + row * SH_ROW_PAD + ch * 4, gsrc + (size_t)c * 4);
                 }
-                asm volatile("cp.async.commit_group;" ::: "memory");
+                cp_async_commit_wait_all();
             }
-            // the block scan + look-back run while the rows are in flight
-            scan = block_scan_lookback(p, tiles, visible, vis_mask, vblock, s_warp, &s_prefix);
-            scanned = true;
-            if (vis_mask != 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
             __syncwarp();
             if (visible) {
                 const float4* rowp = reinterpret_cast<const float4*>(tile + lane * SH_ROW_PAD);
@@ -267,17 +201,10 @@ preprocess_fwd_kernel(const __grid_constant__ PreprocessParams p) {
         }
     }
 
-    if (!scanned) scan = block_scan_lookback(p, tiles, visible, vis_mask, vblock, s_warp, &s_prefix);
     if (in_range) {
         p.radii[idx] = visible ? radius_i : 0;
         p.tiles_touched[idx] = tiles;
-        p.point_offsets[idx] = scan.offset_incl;
-        if (idx == (int64_t)p.P - 1) {
-            p.header->num_rendered = scan.offset_incl;
-            p.header->num_visible = scan.rank + (visible ? 1u : 0u);
-        }
         if (visible) {
-            const uint32_t rank = scan.rank;
             SplatRec r;
             r.q0 = make_float4(img_x, img_y, con_a, con_b);
             r.q1 = make_float4(con_c, p.opacities[idx], rgb.x, rgb.y);
@@ -285,12 +212,9 @@ preprocess_fwd_kernel(const __grid_constant__ PreprocessParams p) {
                                __uint_as_float((uint32_t)rect.x0 | ((uint32_t)rect.y0 << 16)),
                                __uint_as_float((uint32_t)(rect.x1 - rect.x0) |
                                                ((uint32_t)(rect.y1 - rect.y0) << 16)));
-            p.rec[rank] = r;
-            p.vis_keys[rank] = __float_as_uint(depth);
-            p.vis_ranks[rank] = rank;
-            p.rank_to_id[rank] = (uint32_t)idx;
-            p.vis_offsets[rank] = scan.offset_incl;
-            p.clamped[rank] = (uint8_t)clamp_bits;
+            p.rec[idx] = r;
+            p.depth_bits[idx] = __float_as_uint(depth);
+            p.clamped[idx] = (uint8_t)clamp_bits;
         }
     }
 }

@@ -16,7 +16,7 @@
 namespace b200s {
 
 
-constexpr int PB_THREADS = PRE_BLOCK;    // must equal the forward's block: block_base is per forward block
+constexpr int PB_THREADS = 256;
 constexpr int PB_ROW_FLOATS = 48;
 constexpr int PB_ROW_PAD = 52;
 constexpr size_t PB_SMEM_SH16 = (size_t)PB_THREADS * PB_ROW_PAD * sizeof(float);
@@ -87,12 +87,6 @@ preprocess_bwd_kernel(const __grid_constant__ PreprocessBwdParams p) {
     const bool in_range = idx < p.P;
     const bool visible = in_range && p.radii[idx] > 0;
     const uint32_t vis_mask = __ballot_sync(FULL_MASK, visible);
-    // visible rank (the forward wrote records, clamp bits and raw sums by rank): block base + visible before me
-    __shared__ uint32_t s_wcnt[PB_THREADS / 32];
-    if (lane == 0) s_wcnt[warp] = __popc(vis_mask);
-    __syncthreads();
-    uint32_t rank = p.block_base[blockIdx.x] + __popc(vis_mask & lanemask_lt());
-    for (int w = 0; w < warp; ++w) rank += s_wcnt[w];
     const bool use_sh = p.shs != nullptr && p.colors_precomp == nullptr;
 
     float* tile = nullptr;
@@ -135,12 +129,12 @@ preprocess_bwd_kernel(const __grid_constant__ PreprocessBwdParams p) {
                 a9[4] += v1.x; a9[5] += v1.y; a9[6] += v1.z; a9[7] += v1.w; a9[8] += v2.x;
             }
         } else {
-            const float4* s = reinterpret_cast<const float4*>(p.accum + (size_t)rank * ACC_STRIDE);
+            const float4* s = reinterpret_cast<const float4*>(p.accum + (size_t)idx * ACC_STRIDE);
             const float4 v0 = s[0], v1 = s[1], v2 = s[2];
             a9[0] = v0.x; a9[1] = v0.y; a9[2] = v0.z; a9[3] = v0.w;
             a9[4] = v1.x; a9[5] = v1.y; a9[6] = v1.z; a9[7] = v1.w; a9[8] = v2.x;
         }
-        const SplatRec* r = p.rec + rank;
+        const SplatRec* r = p.rec + idx;
         const float4 q0 = r->q0;
         const float con_c = r->q1.x;
         const float con_a = q0.z, con_b = q0.w;
@@ -264,7 +258,7 @@ preprocess_bwd_kernel(const __grid_constant__ PreprocessBwdParams p) {
         }
         if (use_sh) {
             sh_view_dir(mx, my, mz, p.campos[0], p.campos[1], p.campos[2], dir_orig, dir);
-            clamp_bits = p.clamped[rank];
+            clamp_bits = p.clamped[idx];
         }
     }
 
