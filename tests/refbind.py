@@ -191,6 +191,45 @@ class RefR2:
         except Exception:
             pass
 
+    def forward(self, *, bg, means3D, opacities, scales, rotations, viewmatrix, projmatrix, campos, tan_fovx,
+                tan_fovy, W, H, shs, degree=3, scale_modifier=1.0, prefiltered=False, debug=False):
+        """rasterizer2's stripped alpha path, `_C.rasterize_gaussians` with 17 arguments (ext.cpp:16,
+        rasterize_points.cu:27-100): no colors_precomp / cov3D_precomp inputs."""
+        dev = means3D.device
+        P, M = means3D.shape[0], shs.shape[1]
+        out = torch.zeros(3, H, W, dtype=torch.float32, device=dev)
+        radii = torch.zeros(P, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize(dev)
+        R = self.lib.ref_r2_forward(self.h, P, degree, M, _p(bg), W, H, _p(means3D), _p(shs), _p(opacities),
+                                    _p(scales), scale_modifier, _p(rotations), _p(viewmatrix), _p(projmatrix),
+                                    _p(campos), tan_fovx, tan_fovy, int(prefiltered), out.data_ptr(),
+                                    radii.data_ptr(), int(debug))
+        torch.cuda.synchronize(dev)
+        if R < 0:
+            raise RuntimeError("reference rasterizer2 forward failed")
+        self.R, self.P, self.W, self.H, self.M, self.D = R, P, W, H, M, degree
+        return R, out, radii
+
+    def backward(self, *, bg, means3D, radii, shs, scales, rotations, viewmatrix, projmatrix, campos, tan_fovx,
+                 tan_fovy, dL_dpix, scale_modifier=1.0, debug=False):
+        """`_C.rasterize_gaussians_backward` of rasterizer2 (ext.cpp:17, rasterize_points.cu:105-180): returns the
+        binding's 6-tuple (dL_dmeans2D, dL_dopacity, dL_dmeans3D, dL_dsh, dL_dscales, dL_drotations) (:177)."""
+        dev = means3D.device
+        P, M = self.P, self.M
+        z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)  # noqa: E731
+        g2d, gcon, gop, gcol, g3d, gcov, gsh, gs, gr = (z(P, 3), z(P, 2, 2), z(P, 1), z(P, 3), z(P, 3), z(P, 6),
+                                                         z(P, M, 3), z(P, 3), z(P, 4))
+        torch.cuda.synchronize(dev)
+        rc = self.lib.ref_r2_backward(self.h, P, self.D, M, self.R, _p(bg), self.W, self.H, _p(means3D), _p(shs),
+                                      _p(scales), scale_modifier, _p(rotations), _p(viewmatrix), _p(projmatrix),
+                                      _p(campos), tan_fovx, tan_fovy, radii.data_ptr(), dL_dpix.data_ptr(),
+                                      g2d.data_ptr(), gcon.data_ptr(), gop.data_ptr(), gcol.data_ptr(), g3d.data_ptr(),
+                                      gcov.data_ptr(), gsh.data_ptr(), gs.data_ptr(), gr.data_ptr(), int(debug))
+        torch.cuda.synchronize(dev)
+        if rc != 0:
+            raise RuntimeError("reference rasterizer2 backward failed")
+        return g2d, gop, g3d, gsh, gs, gr
+
     def getidxmap(self, *, means3D, normal, scales, rotations, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                   feature_vector, shs, campos, W, H, debug=False):
         dev = means3D.device

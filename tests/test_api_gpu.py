@@ -159,6 +159,43 @@ def test_idxmap_matches_reference_rasterizer2(dev, cfg_name):
     r2.close()
 
 
+@pytest.mark.skipif(not refbind.available("ref_r2"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("cfg_name", ["T1", "C1"])
+def test_rasterizer2_alpha_exports_match_reference(dev, cfg_name):
+    """rasterizer2's C-level alpha path — the 17-argument `rasterize_gaussians` and the
+    6-tuple `rasterize_gaussians_backward` (rasterizer2/ext.cpp:16-17, rasterize_points.cu:27,105) — against the
+    reference rasterizer2 compiled for sm_100 (oracle/ref_shim_r2.cu: ref_r2_forward / ref_r2_backward)."""
+    from neuralgaussiansplatting_b200 import rasterizer2 as r2mod
+    from neuralgaussiansplatting_b200.synthetic import make_grad_image
+    cfg, sc, cam = Hh.scene_on(cfg_name, dev)
+    bg = torch.tensor([0.1, 0.2, 0.3], device=dev)
+    tx, ty = math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5)
+    out = r2mod.alpha_forward(bg, sc["means3D"], sc["opacities"], sc["scales"], sc["rotations"], 1.0,
+                              cam.world_view_transform, cam.full_proj_transform, tx, ty, cfg.height, cfg.width,
+                              sc["shs"], 3, cam.camera_center, False, False)
+    assert len(out) == 6                                              # (R, color, radii, geom, binning, img)
+    R, color, radii, geom, binning, img = out
+    r2 = refbind.RefR2()
+    rR, rcolor, rradii = r2.forward(bg=bg, means3D=sc["means3D"], opacities=sc["opacities"], scales=sc["scales"],
+                                    rotations=sc["rotations"], viewmatrix=cam.world_view_transform,
+                                    projmatrix=cam.full_proj_transform, campos=cam.camera_center, tan_fovx=tx,
+                                    tan_fovy=ty, W=cfg.width, H=cfg.height, shs=sc["shs"])
+    assert R == rR and torch.equal(radii, rradii)
+    assert float((color - rcolor).abs().max()) < 1e-5
+    dL = make_grad_image(cfg, 0, device=dev)
+    g = r2mod.alpha_backward(bg, sc["means3D"], radii, sc["scales"], sc["rotations"], 1.0, cam.world_view_transform,
+                             cam.full_proj_transform, tx, ty, dL, sc["shs"], 3, cam.camera_center, geom, R, binning,
+                             img, False)
+    gr = r2.backward(bg=bg, means3D=sc["means3D"], radii=rradii, shs=sc["shs"], scales=sc["scales"],
+                     rotations=sc["rotations"], viewmatrix=cam.world_view_transform,
+                     projmatrix=cam.full_proj_transform, campos=cam.camera_center, tan_fovx=tx, tan_fovy=ty,
+                     dL_dpix=dL)
+    assert len(g) == 6 and [tuple(t.shape) for t in g] == [tuple(t.shape) for t in gr]
+    for name, a, b in zip(("means2D", "opacity", "means3D", "sh", "scales", "rotations"), g, gr):
+        assert Hh.rel_l2(a, b) < 1e-4, name
+    r2.close()
+
+
 def test_idxmap_module_autograd_contract(dev):
     cfg, sc, cam = Hh.scene_on("T0", dev)
     pc = SyntheticGaussians(sc, requires_grad=True)
