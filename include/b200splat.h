@@ -264,7 +264,10 @@ int b200s_count_pairs(const B200sForwardArgs* args, unsigned long long* counts_d
  *      peer_flags[r] : rank r's flag array (u32, >= b200s_peer_allreduce_flag_bytes, zeroed
  *                      once at allocation), same mapping rules.
  *      multicast_buf : NVSwitch multicast mapping of the buffer or NULL; used only when
- *                      use_multimem != 0 (multimem.ld_reduce / multimem.st; the switch sums).
+ *                      use_multimem != 0. Bit 0: the summed prefix goes through multimem.ld_reduce /
+ *                      multimem.st (the switch sums, in ITS order: replicas identical, not the
+ *                      rank-order sum). Bit 1: the all-gather slots are PUSHED with multimem.st (a pure
+ *                      copy, exact) instead of pulled with peer loads.
  *      epoch         : strictly increasing per call (1, 2, ...) — flags are never reset.
  *      In-place: after the call (stream-ordered) every rank's buffer holds the sum. */
 #define B200S_MAX_PEERS 16

@@ -377,7 +377,7 @@ extern "C" size_t b200s_peer_allreduce_vis_bytes(int32_t rows, int32_t world) {
 extern "C" int b200s_peer_allreduce_sum_f32(const B200sPeerReduceArgs* a, b200s_stream_t stream_) {
     if (!a || a->world < 1 || a->world > B200S_MAX_PEERS || a->rank < 0 || a->rank >= a->world) return B200S_E_BADARG;
     if (a->ctas < 1 || a->ctas > 1024 || (a->n_floats & 3u) || a->epoch == 0) return B200S_E_BADARG;
-    if (a->use_multimem && !a->multicast_buf) return B200S_E_BADARG;
+    if ((a->use_multimem & 3) && !a->multicast_buf) return B200S_E_BADARG;
     for (int r = 0; r < a->world; ++r)
         if (!a->peer_bufs[r] || !a->peer_flags[r] || ((uintptr_t)a->peer_bufs[r] & 15u)) return B200S_E_BADARG;
     if (a->radii) {

@@ -49,6 +49,7 @@ struct PeerReduceParams {
     size_t vis_off;        // byte offset of the visibility array from bufs[r]
     // all-gather region: slot r (gslot4 float4) at goff4 + r*gslot4 of every buffer ends up holding rank r's data
     size_t goff4, gslot4;
+    int gather_push;       // 1: every rank multimem.st's its own slot through the NVSwitch multicast mapping
 };
 
 constexpr unsigned long long PR_BARRIER_TIMEOUT_NS = 60ull * 1000000000ull;   // peers start within a minute or never
@@ -155,6 +156,30 @@ __device__ __forceinline__ void peer_gather_slots(const PeerReduceParams& p, int
     }
 }
 
+// The same all-gather as a PUSH through the NVSwitch multicast mapping: each rank streams its own slot from local
+// memory into `multimem.st`, the switch replicates every 16 bytes to all peers. Per GPU 1 x slot leaves and
+// (world-1) x slot arrives, no read round trips over NVLink and 1/(world-1) of the pull's SM work.
+__device__ __forceinline__ void peer_gather_push(const PeerReduceParams& p) {
+    constexpr int UP = 8;
+    const size_t stride = (size_t)gridDim.x * PR_THREADS;
+    const size_t off = p.goff4 + (size_t)p.rank * p.gslot4;
+    const float4* src = p.bufs[p.rank] + off;
+    float4* dst = p.mc + off;
+    for (size_t i0 = (size_t)blockIdx.x * PR_THREADS + threadIdx.x; i0 < p.gslot4; i0 += stride * UP) {
+        float4 v[UP];
+#pragma unroll
+        for (int u = 0; u < UP; ++u) {
+            const size_t i = i0 + u * stride;
+            if (i < p.gslot4) v[u] = ld_peer(src + i);
+        }
+#pragma unroll
+        for (int u = 0; u < UP; ++u) {
+            const size_t i = i0 + u * stride;
+            if (i < p.gslot4) multimem_st(dst + i, v[u]);
+        }
+    }
+}
+
 template <int WORLD, bool MULTIMEM, bool SPARSE>
 __global__ void __launch_bounds__(PR_THREADS)
 peer_allreduce_kernel(const __grid_constant__ PeerReduceParams p) {
@@ -174,6 +199,8 @@ peer_allreduce_kernel(const __grid_constant__ PeerReduceParams p) {
             }
     }
     peer_barrier(p, 0);
+    // the pushed slots travel while the dense part is summed (stores are fire-and-forget)
+    if (p.gslot4 != 0 && p.gather_push) peer_gather_push(p);
 
     const size_t n4 = SPARSE ? p.sparse_off4 : p.n4;     // densely reduced part
     const size_t per = (n4 + world - 1) / world;
@@ -240,7 +267,7 @@ peer_allreduce_kernel(const __grid_constant__ PeerReduceParams p) {
         }
     }
 
-    if (p.gslot4 != 0) peer_gather_slots(p, world);
+    if (p.gslot4 != 0 && !p.gather_push) peer_gather_slots(p, world);
 
     if constexpr (SPARSE && WORLD > 0) {
         __shared__ uint32_t smask[PR_CHUNK / 4];        // one byte per row: bit r = visible on rank r
@@ -311,8 +338,9 @@ int launch_peer_allreduce(const B200sPeerReduceArgs& a, cudaStream_t stream) {
     p.rank = a.rank; p.world = a.world; p.epoch = a.epoch;
     p.goff4 = (size_t)(a.gather_offset_floats / 4);
     p.gslot4 = (size_t)(a.gather_floats / 4);
+    p.gather_push = (a.use_multimem & 2) && a.multicast_buf != nullptr;
     const int ctas = a.ctas;
-    if (a.use_multimem) return launch_pr<0, true>(p, ctas, stream);
+    if (a.use_multimem & 1) return launch_pr<0, true>(p, ctas, stream);
     if (a.radii && a.sparse_rows > 0) {
         p.radii = (const int*)a.radii;
         p.rows = a.sparse_rows;

@@ -309,9 +309,11 @@ class PeerGradientAllReduce:
     # thread keeps 16 loads in flight of which (world-1)/world are remote; more CTAs only take SMs from the
     # rasterizer that runs concurrently.
     AUTO_CTAS = {2: 16, 3: 16, 4: 12}
+    AUTO_CTAS_FACTORED = {2: 16, 3: 16, 4: 16}     # default 16: the payload is 2.5x smaller but latency-bound
 
     def __init__(self, P: int, sh_coeffs: int = 16, device=None, group=None, n_buffers: int = 2, ctas: int = 0,
-                 multimem: bool = False, backend: str = "auto", factored: bool = True):
+                 multimem: bool = False, backend: str = "auto", factored: bool = True, gather_push: bool = True,
+                 priority: int = -1):
         from . import _lib
         self._libmod = _lib
         self._lib = _lib.load()
@@ -331,7 +333,8 @@ class PeerGradientAllReduce:
         self.slot_floats = -(-(3 * int(P) + 4) // 64) * 64
         self.gather_floats_total = self.world * self.slot_floats if self.factored else 0
         self.n_buffers = int(n_buffers)
-        self.ctas = int(ctas) if ctas and ctas > 0 else self.AUTO_CTAS.get(self.world, 8)
+        self.ctas = int(ctas) if ctas and ctas > 0 else (
+            self.AUTO_CTAS_FACTORED.get(self.world, 16) if factored else self.AUTO_CTAS.get(self.world, 8))
         self.flag_bytes = -(-int(self._lib.b200s_peer_allreduce_flag_bytes(self.ctas, self.world)) // 256) * 256
         self.buf_bytes = (self.n_floats + self.gather_floats_total) * 4
         self.P, self.sh_coeffs = int(P), int(sh_coeffs)
@@ -343,12 +346,15 @@ class PeerGradientAllReduce:
         torch.cuda.synchronize(self.device)
         dist.barrier(group=group)                      # nobody raises a flag before every flag array is zero
         self.multimem = bool(multimem) and self.mem.multicast_ptr != 0
+        # factored mode: push the factor slots through the NVSwitch multicast mapping (multimem.st, an exact copy)
+        # when the box has one; otherwise every rank pulls the foreign slots with peer loads
+        self.gather_push = bool(gather_push) and self.factored and self.mem.multicast_ptr != 0
         self._flat = [self.mem.local[self.flag_bytes + i * self.slot_bytes:
                                      self.flag_bytes + i * self.slot_bytes + self.buf_bytes]
                       .view(torch.float32) for i in range(self.n_buffers)]
         self._cur = -1
         self._epoch = 0
-        self._stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self._stream = torch.cuda.Stream(device=self.device, priority=int(priority))
         self._done: Optional[torch.cuda.Event] = None
         self._copy_back = None
         self._factors_fresh = False
@@ -421,7 +427,8 @@ class PeerGradientAllReduce:
         for r in range(self.world):
             a.peer_bufs[r] = self.mem.ptrs[r] + off
             a.peer_flags[r] = self.mem.ptrs[r]
-        a.multicast_buf = (self.mem.multicast_ptr + off) if self.multimem else None
+        push = self.gather_push and use_factored
+        a.multicast_buf = (self.mem.multicast_ptr + off) if (self.multimem or push) else None
         a.n_floats = self.dense_floats if use_factored else self.n_floats
         if use_factored:
             a.gather_offset_floats, a.gather_floats = self.n_floats, self.slot_floats
@@ -429,7 +436,7 @@ class PeerGradientAllReduce:
         self._epoch += 1
         a.epoch = self._epoch
         a.ctas = self.ctas
-        a.use_multimem = int(self.multimem)
+        a.use_multimem = int(self.multimem) | (2 if push else 0)
         ready = torch.cuda.Event()
         ready.record(torch.cuda.current_stream(self.device))
         self._stream.wait_event(ready)
