@@ -60,6 +60,8 @@ class ViewParallelTrainer:
         self.stats = parallel.DensificationStats(self.P, self.dev)
         self.iteration = 0
         self._E = torch.Tensor([])
+        # the rasterizer runs at high priority, the collective's side stream at normal priority (parallel.py)
+        self.compute_stream = torch.cuda.Stream(device=self.dev, priority=-1) if self.world > 1 else None
 
     # ------------------------------------------------------------------ one view: forward, loss, backward
     def _view(self, camera, gt_image, tan_fovx, tan_fovy):
@@ -82,6 +84,12 @@ class ViewParallelTrainer:
         import math
         if not isinstance(cameras, (list, tuple)):
             cameras, gt_images = [cameras], [gt_images]
+        if self.compute_stream is not None and torch.cuda.current_stream(self.dev) != self.compute_stream:
+            self.compute_stream.wait_stream(torch.cuda.current_stream(self.dev))
+            with torch.cuda.stream(self.compute_stream):
+                out = self.step(cameras, gt_images)
+            torch.cuda.current_stream(self.dev).wait_stream(self.compute_stream)
+            return out
         self.iteration += 1
         peer = isinstance(self.reducer, parallel.PeerGradientAllReduce)
         total, loss3 = None, None

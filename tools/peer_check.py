@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--backend", default="auto")
     ap.add_argument("--quick", action="store_true", help="exactness checks only")
+    ap.add_argument("--only-factored", action="store_true", help="time the factored variants only")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -161,10 +162,13 @@ def main():
     g = torch.Generator(device=dev).manual_seed(7 + rank)
     radii43 = (torch.rand(a.P, device=dev, generator=g) < 0.43).to(torch.int32)
     means_big = torch.randn(a.P, 3, device=dev, generator=torch.Generator(device=dev).manual_seed(1))
-    for mm, fct in ((False, True), (True, True), (False, False), ("sparse", False), (True, False)):
+    variants = [(False, True, True), (False, True, False), (True, True, True)]
+    if not a.only_factored:
+        variants += [(False, False, False), ("sparse", False, False), (True, False, False)]
+    for mm, fct, push in variants:
         for ctas in (4, 8, 16, 32):
             red = parallel.PeerGradientAllReduce(a.P, 16, dev, ctas=ctas, multimem=(mm is True), n_buffers=1,
-                                                 backend=a.backend, factored=fct)
+                                                 backend=a.backend, factored=fct, gather_push=push)
             if mm is True and not red.multimem:
                 del red
                 break
@@ -187,7 +191,8 @@ def main():
                     red.start(None, radii=rad)
                 red.wait()
             ms = time_it(fn, a.iters)
-            name = ("factored_" if fct else "") + ("multimem" if mm is True else "sparse43" if mm else "p2p")
+            name = ("factored_" + ("push_" if red.gather_push else "pull_") if fct else "") + (
+                "multimem" if mm is True else "sparse43" if mm else "p2p")
             times[f"{name}_ctas{ctas}"] = {"ms": round(ms, 4), "algbw_GBps": round(nbytes / ms / 1e6, 1)}
             del red
             torch.cuda.empty_cache()
