@@ -840,32 +840,51 @@ def render_only(args, rank, world, dev, impl):
                                H=cfg.height, shs=sc["shs"], scales=sc["scales"], rotations=sc["rotations"])[1]
         closer = ref.close
 
-    def resident_pass(_s):
-        for v in mine:
-            c = cams[v]
-            render(c.world_view_transform, c.full_proj_transform, c.camera_center)
-
-    img_host = [torch.empty(3, cfg.height, cfg.width).pin_memory() for _ in range(2)]
-    img_ev = [None, None]
-    img_keep = [None, None]
-    cam_dev = [torch.empty(35, device=dev) for _ in range(2)]
-    copy_stream = torch.cuda.Stream(device=dev)
+    RB = max(1, args.render_batch) if impl == "ours" else 1
+    batches = [mine[i:i + RB] for i in range(0, len(mine), RB)]
+    img_dev = [torch.empty(RB, 3, cfg.height, cfg.width, device=dev) for _ in range(2)] if impl == "ours" else None
     cnt = {"n": 0}
 
-    def e2e_pass(_s):
-        for v in mine:
+    def render_views(vs, views_proj_campos, out):
+        """ours: ONE batched call (renderer.render_batch's path: shared workspace, one host sync per batch);
+        reference: its forward per view, as render.py:31-32 loops."""
+        if impl == "ours":
+            _C.rasterize_gaussians_batch(bg, sc["means3D"], E, sc["opacities"], sc["scales"], sc["rotations"], 1.0, E,
+                                         views_proj_campos, tan[0], tan[1], cfg.height, cfg.width, sc["shs"], 3, False,
+                                         out_color=out[:len(vs)])
+            return out[:len(vs)]
+        return torch.stack([render(*vpc) for vpc in views_proj_campos]) if len(vs) > 1 else render(*views_proj_campos[0])[None]
+
+    def resident_pass(_s):
+        for vs in batches:
             i = cnt["n"] & 1
             cnt["n"] += 1
+            cams_b = [(cams[v].world_view_transform, cams[v].full_proj_transform, cams[v].camera_center) for v in vs]
+            render_views(vs, cams_b, img_dev[i] if img_dev is not None else None)
+
+    img_host = [torch.empty(RB, 3, cfg.height, cfg.width).pin_memory() for _ in range(2)]
+    img_ev = [None, None]
+    img_keep = [None, None]
+    cam_dev = [torch.empty(RB, 35, device=dev) for _ in range(2)]
+    cam_host_b = {tuple(vs): torch.stack([cam_host[v] for v in vs]).pin_memory() for vs in batches}
+    copy_stream = torch.cuda.Stream(device=dev)
+
+    def e2e_pass(_s):
+        for vs in batches:
+            i = cnt["n"] & 1
+            cnt["n"] += 1
+            n = len(vs)
             cd = cam_dev[i]
-            cd.copy_(cam_host[v], non_blocking=True)
-            img = render(cd[0:16].view(4, 4), cd[16:32].view(4, 4), cd[32:35])
-            rendered = torch.cuda.Event()
-            rendered.record(torch.cuda.current_stream(dev))
+            cd[:n].copy_(cam_host_b[tuple(vs)], non_blocking=True)
             if img_ev[i] is not None:
                 img_ev[i].synchronize()          # the host consumed (here: may overwrite) this pinned buffer
-            with torch.cuda.stream(copy_stream):     # image k goes to the host while view k+1 is rasterized
+            img = render_views(vs, [(cd[j, 0:16].view(4, 4), cd[j, 16:32].view(4, 4), cd[j, 32:35]) for j in range(n)],
+                               img_dev[i] if img_dev is not None else None)
+            rendered = torch.cuda.Event()
+            rendered.record(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(copy_stream):     # batch k goes to the host while batch k+1 is rasterized
                 copy_stream.wait_event(rendered)
-                img_host[i].copy_(img, non_blocking=True)
+                img_host[i][:n].copy_(img, non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(copy_stream)
             img.record_stream(copy_stream)
@@ -895,7 +914,9 @@ def render_only(args, rank, world, dev, impl):
                     "what": "camera block H2D + rendered image D2H to pinned host memory per view on a copy stream (image k "
                             "leaves while view k+1 is rasterized), double-buffered; "
                             "no gather to rank 0 (every rank keeps / writes its own views, as render.py does per view)"},
-            "impl": impl}
+            "impl": impl,
+            "api": (f"_C.rasterize_gaussians_batch, {RB} views per call: one shared workspace, one host sync per batch"
+                    if impl == "ours" else "reference forward per view (render.py:31-32)")}
 
 
 # ----------------------------------------------------------------------------------------- main
@@ -927,6 +948,8 @@ def main():
                          "CTAs only take SM slots the rasterizer leaves free (measured at 2 GPUs: 1.93 vs 2.06 ms/step)")
     ap.add_argument("--no-render-only", action="store_true", help="skip the C4 render-only block")
     ap.add_argument("--render-passes", type=int, default=2, help="timed passes over the 64 C4 views")
+    ap.add_argument("--render-batch", type=int, default=8,
+                    help="our arm, render-only: views per _C.rasterize_gaussians_batch call (one host sync per batch)")
     ap.add_argument("--blend-mode", default="strict", choices=["strict", "fast"],
                     help="our arm: strict = expf (bit-exact n_contrib, the parity gate); fast = ex2.approx falloff")
     ap.add_argument("--allreduce", default="overlap", choices=["overlap", "blocking"],

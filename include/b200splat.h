@@ -117,6 +117,14 @@ int b200s_forward_render(const B200sForwardArgs* args, b200s_stream_t stream);
 int b200s_forward(const B200sForwardArgs* args, b200s_stream_t stream);
 /* Asynchronous copy of the header into (pinned) host memory. */
 int b200s_read_header(const void* geom_ws, B200sHeader* header_host, b200s_stream_t stream);
+/* View batch (the loop of render.py:24-35 / the view loop of train.py:75-93 without gradients):
+ * `count` forwards enqueued back to back on one stream with NO host synchronisation in between. The views may
+ * (and normally do) share ONE geometry / image / binning workspace — they run in stream order — and differ in
+ * camera, out_color and radii pointers. After view i its header is copied into headers_host[i] (pinned memory);
+ * the caller synchronises ONCE after the call and then checks every header: `error`, and `overflow` /
+ * num_rendered > bin_capacity (that view rendered nothing: re-run it alone with a larger binning workspace). */
+int b200s_forward_batch(const B200sForwardArgs* views, int32_t count, B200sHeader* headers_host,
+                        b200s_stream_t stream);
 
 /* ---- backward: replaces CudaRasterizer::Rasterizer::backward
  *      (rasterizer_impl.cu:340-434) and RasterizeGaussiansBackwardCUDA

@@ -131,6 +131,7 @@ def flush_errors() -> None:
 
 
 overflow_count = 0     # optimistic-capacity overflows since import (each one re-runs expand + sort + blend)
+sync_count = 0         # host synchronisations issued by the forward paths of this module (tests / tuning)
 
 
 def _raise_header_error(error: int, where: str = ""):
@@ -142,6 +143,8 @@ def _read_header(lib, geom: torch.Tensor, device) -> "_lib.Header":
     buf, hdr = _pinned_header()
     _lib.check(lib.b200s_read_header(geom.data_ptr(), buf.data_ptr(), _stream(device)), "b200s_read_header")
     torch.cuda.current_stream(device).synchronize()
+    global sync_count
+    sync_count += 1
     if hdr.error:
         raise RuntimeError(f"b200splat device error flags 0x{hdr.error:x}"
                            + (" (point filtered although prefiltered is set)" if hdr.error & 2 else ""))
@@ -186,6 +189,7 @@ def _forward_impl(background, means3D, colors, opacity, scales, rotations, scale
 
     Returns (num_rendered:int, out_color[3,H,W] f32, radii[P] i32, geomBuffer u8, binningBuffer u8, imgBuffer u8).
     The three buffers are opaque, as in the reference (their layout is private to the library)."""
+    global sync_count, overflow_count
     if means3D.ndimension() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     dev = _require_cuda(means3D)
@@ -231,6 +235,7 @@ def _forward_impl(background, means3D, colors, opacity, scales, rotations, scale
             _lib.check(lib.b200s_forward_render(C.byref(a), stream), "b200s_forward_render")
             deferred.queue(lib, geom.data_ptr(), dev, "forward")
             ready.synchronize()                        # scan done: sort + blend of this view are still in flight
+            sync_count += 1
             if hdr.error:
                 _raise_header_error(hdr.error)
             if int(hdr.num_rendered) > int(a.bin_capacity):      # the device made stage 2 a no-op: redo it exactly
@@ -247,7 +252,6 @@ def _forward_impl(background, means3D, colors, opacity, scales, rotations, scale
         num_rendered = int(hdr.num_rendered)
         if binning is None:
             if hint is not None:
-                global overflow_count
                 overflow_count += 1
             binning = alloc_bin(num_rendered)
             _lib.check(lib.b200s_forward_render(C.byref(a), stream), "b200s_forward_render")
@@ -257,6 +261,97 @@ def _forward_impl(background, means3D, colors, opacity, scales, rotations, scale
         # overflow (and silently re-run expand + sort + blend) on every large one
         _capacity_hint[key] = max(num_rendered, int(0.98 * _capacity_hint.get(key, 0)))
     return (num_rendered, out_color, radii, geom, binning, img), a, keep
+
+
+def rasterize_gaussians_batch(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                              cameras, tan_fovx, tan_fovy, image_height, image_width, sh, degree, prefiltered=False,
+                              out_color: Optional[torch.Tensor] = None):
+    """B forwards of the same Gaussians for B cameras — the view loop of render.py:24-35 — with ONE geometry /
+    image / binning workspace shared by all views, the images written straight into `out_color` [B,3,H,W], and ONE
+    host synchronisation per batch (b200s_forward_batch): the per-view headers are queued into pinned memory and
+    checked together. No gradient state is kept (use rasterize_gaussians per view for training).
+
+    cameras: sequence of (viewmatrix[4,4], projmatrix[4,4], campos[3]) device tensors; tan_fovx / tan_fovy: floats or
+    per-view sequences. Returns (num_rendered: list[int], out_color [B,3,H,W], radii int32 [B,P])."""
+    global sync_count, overflow_count
+    if means3D.ndimension() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    dev = _require_cuda(means3D)
+    lib = _lib.load()
+    B, P, H, W = len(cameras), means3D.size(0), int(image_height), int(image_width)
+    tx = list(tan_fovx) if isinstance(tan_fovx, (list, tuple)) else [float(tan_fovx)] * B
+    ty = list(tan_fovy) if isinstance(tan_fovy, (list, tuple)) else [float(tan_fovy)] * B
+    with torch.cuda.device(dev):
+        if out_color is None:
+            out_color = torch.empty((B, NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
+        elif (tuple(out_color.shape) != (B, NUM_CHANNELS, H, W) or out_color.dtype != torch.float32
+              or out_color.device != dev or not out_color.is_contiguous()):
+            raise RuntimeError(f"out_color must be a contiguous float32 [{B},3,{H},{W}] tensor on {dev}")
+        radii = torch.empty((B, P), dtype=torch.int32, device=dev)
+        if B == 0:
+            return [], out_color, radii
+        if P == 0:
+            out_color.zero_()
+            return [0] * B, out_color, radii
+        u8 = dict(dtype=torch.uint8, device=dev)
+        key = (dev.index, P, W, H)
+        first = 0
+        nums = [0] * B
+        if _capacity_hint.get(key) is None:
+            # no capacity estimate for this shape yet: the first view takes the exact (synchronising) path
+            v, pj, cp = cameras[0]
+            o = rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                    cov3D_precomp, v, pj, tx[0], ty[0], H, W, sh, degree, cp, prefiltered, False)
+            nums[0] = o[0]
+            out_color[0].copy_(o[1]); radii[0].copy_(o[2])
+            first = 1
+            if B == 1:
+                return nums, out_color, radii
+        hint = _capacity_hint[key]
+        geom = torch.empty(lib.b200s_geometry_workspace_size(P), **u8)
+        img = torch.empty(lib.b200s_image_workspace_size(W, H), **u8)
+        nbytes = lib.b200s_binning_workspace_size(max(int(hint * config["growth"]) + 4096, 1), W, H)
+        binning = torch.empty(nbytes, **u8)
+        capacity = lib.b200s_binning_capacity_for_bytes(nbytes)
+        n = B - first
+        views = (_lib.ForwardArgs * n)()
+        keep = []
+        for j in range(n):
+            b = first + j
+            v, pj, cp = cameras[b]
+            a, kp = _fill_forward_args(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                       cov3D_precomp, v, pj, tx[b], ty[b], H, W, sh, degree, cp, prefiltered, False)
+            keep.append(kp)
+            a.out_color, a.radii = out_color[b].data_ptr(), radii[b].data_ptr()
+            a.geom_ws, a.geom_bytes = geom.data_ptr(), geom.numel()
+            a.img_ws, a.img_bytes = img.data_ptr(), img.numel()
+            a.bin_ws, a.bin_bytes, a.bin_capacity = binning.data_ptr(), nbytes, capacity
+            views[j] = a
+        hdrs = getattr(_tls, "batch_hdrs", None)
+        if hdrs is None or hdrs.numel() < n * C.sizeof(_lib.Header):
+            hdrs = _tls.batch_hdrs = torch.zeros(max(n, 16) * C.sizeof(_lib.Header), dtype=torch.uint8).pin_memory()
+        stream = _stream(dev)
+        _deferred().poll()
+        _lib.check(lib.b200s_forward_batch(C.addressof(views), n, hdrs.data_ptr(), stream), "b200s_forward_batch")
+        torch.cuda.current_stream(dev).synchronize()           # the ONE synchronisation of the batch
+        sync_count += 1
+        redo = []
+        for j in range(n):
+            h = _lib.Header.from_address(hdrs.data_ptr() + j * C.sizeof(_lib.Header))
+            if h.error:
+                _raise_header_error(h.error, f" (view {first + j} of the batch)")
+            nums[first + j] = int(h.num_rendered)
+            if h.overflow or int(h.num_rendered) > capacity:
+                redo.append(first + j)
+        for b in redo:                                          # capacity estimate too small for these views: exact re-run
+            overflow_count += 1
+            v, pj, cp = cameras[b]
+            o = rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                    cov3D_precomp, v, pj, tx[b], ty[b], H, W, sh, degree, cp, prefiltered, True)
+            out_color[b].copy_(o[1]); radii[b].copy_(o[2])
+        _capacity_hint[key] = max(max(nums), int(0.98 * _capacity_hint.get(key, 0)))
+        del keep
+    return nums, out_color, radii
 
 
 def _backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,

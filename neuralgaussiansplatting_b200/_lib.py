@@ -158,6 +158,7 @@ SYMBOLS = [
     ("b200s_forward_render", C.c_int, [C.POINTER(ForwardArgs), C.c_void_p]),
     ("b200s_forward", C.c_int, [C.POINTER(ForwardArgs), C.c_void_p]),
     ("b200s_read_header", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    ("b200s_forward_batch", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     ("b200s_backward", C.c_int, [C.POINTER(BackwardArgs), C.c_void_p]),
     ("b200s_mark_visible", C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("b200s_idxmap_workspace_size", C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),

@@ -261,6 +261,22 @@ int b200s_read_header(const void* geom_ws, B200sHeader* header_host, b200s_strea
     return 0;
 }
 
+int b200s_forward_batch(const B200sForwardArgs* views, int32_t count, B200sHeader* headers_host,
+                        b200s_stream_t stream) {
+    if (count < 0 || (count > 0 && (!views || !headers_host))) return B200S_E_BADARG;
+    for (int32_t i = 0; i < count; ++i) {
+        int rc = b200s_forward(&views[i], stream);
+        if (rc) return rc;
+        if (views[i].P > 0) {
+            rc = b200s_read_header(views[i].geom_ws, &headers_host[i], stream);
+            if (rc) return rc;
+        } else {
+            memset(&headers_host[i], 0, sizeof(B200sHeader));
+        }
+    }
+    return 0;
+}
+
 int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (!a) return B200S_E_BADARG;

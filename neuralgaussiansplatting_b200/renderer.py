@@ -91,12 +91,44 @@ def render_idxmap(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_mo
 
 def render_batch(cameras: Sequence, pc, pipe, bg_color: torch.Tensor, scaling_modifier: float = 1.0,
                  out: Optional[torch.Tensor] = None) -> Dict[str, object]:
-    """Render a list of views back to back. Returns {"render": [B,3,H,W], "radii": [B,P], "views": [dict,...]}.
-    All views must share the image size for the stacked outputs; per-view dicts are returned regardless."""
+    """Render a list of views back to back (the loop of render.py:24-35, gaussian_renderer.render() per view).
+    Returns {"render": [B,3,H,W], "radii": [B,P], "num_rendered": [B ints], "views": [dict, ...]}.
+
+    Without gradients (torch.no_grad(), or no input requires grad) and with equal image sizes this is ONE batched
+    call: `_C.rasterize_gaussians_batch` shares one geometry / image / binning workspace between the views, writes
+    every image straight into `out` / the returned [B,3,H,W] tensor and synchronises the host ONCE per batch.
+    When gradients are needed every view keeps its own state buffers for its backward, so the views go through
+    `render()` one by one (their forward still never blocks mid-pipeline)."""
+    cameras = list(cameras)
+    sizes = {(int(c.image_height), int(c.image_width)) for c in cameras}
+    needs_grad = torch.is_grad_enabled() and any(
+        t is not None and t.requires_grad for t in (pc.get_xyz, pc.get_features, pc.get_opacity, pc.get_scaling,
+                                                    pc.get_rotation))
+    if cameras and len(sizes) == 1 and not needs_grad and not pipe.debug:
+        from . import _C
+        H, W = next(iter(sizes))
+        E = torch.Tensor([])
+        xyz = pc.get_xyz.detach()
+        colors, shs, cov = E, E, E
+        scales, rots = E, E
+        if pipe.compute_cov3D_python:
+            cov = pc.get_covariance(scaling_modifier).detach()
+        else:
+            scales, rots = pc.get_scaling.detach(), pc.get_rotation.detach()
+        if pipe.convert_SHs_python:
+            raise NotImplementedError("render_batch: convert_SHs_python makes colours per view; use render() per view")
+        shs = pc.get_features.detach()
+        nums, img, radii = _C.rasterize_gaussians_batch(
+            bg_color, xyz, colors, pc.get_opacity.detach(), scales, rots, scaling_modifier, cov,
+            [(c.world_view_transform, c.full_proj_transform, c.camera_center) for c in cameras],
+            [math.tan(c.FoVx * 0.5) for c in cameras], [math.tan(c.FoVy * 0.5) for c in cameras], H, W, shs,
+            pc.active_sh_degree, False, out_color=out)
+        views = [{"render": img[b], "viewspace_points": None, "visibility_filter": radii[b] > 0, "radii": radii[b]}
+                 for b in range(len(cameras))]
+        return {"render": img, "radii": radii, "num_rendered": nums, "views": views}
     views: List[Dict[str, torch.Tensor]] = [render(c, pc, pipe, bg_color, scaling_modifier) for c in cameras]
-    same = len({(v["render"].shape) for v in views}) == 1
     res: Dict[str, object] = {"views": views}
-    if same and views:
+    if len(sizes) == 1 and views:
         if out is not None:
             torch.stack([v["render"] for v in views], out=out)
             res["render"] = out

@@ -116,6 +116,66 @@ def test_render_batch_matches_single_views(dev):
         assert torch.equal(res["render"][v], single["render"]) and torch.equal(res["radii"][v], single["radii"])
 
 
+def test_render_batch_shares_one_workspace_and_synchronises_once(dev):
+    """B views back to back, one workspace, images written into the caller's [B,3,H,W] tensor,
+    exactly ONE host synchronisation per batch once the capacity estimate for the shape exists."""
+    cfg, sc, _ = Hh.scene_on("T1", dev)
+    bg = torch.tensor([0.1, 0.2, 0.3], device=dev)
+    pc = SyntheticGaussians(sc)
+    cams = [make_camera(cfg, v, device=dev) for v in range(6)]
+    with torch.no_grad():
+        render_batch(cams[:2], pc, PipelineParams(), bg)                  # learns the capacity estimate
+        out = torch.full((6, 3, cfg.height, cfg.width), float("nan"), device=dev)
+        s0, o0 = _C.sync_count, _C.overflow_count
+        res = render_batch(cams, pc, PipelineParams(), bg, out=out)
+        assert _C.sync_count - s0 == 1 and _C.overflow_count == o0
+    assert res["render"].data_ptr() == out.data_ptr() and torch.isfinite(out).all()
+    assert len(res["num_rendered"]) == 6 and all(n > 0 for n in res["num_rendered"])
+    for v, cam in enumerate(cams):
+        single = render(cam, pc, PipelineParams(), bg)
+        assert torch.equal(out[v], single["render"]) and torch.equal(res["radii"][v], single["radii"])
+        assert torch.equal(res["views"][v]["visibility_filter"], single["visibility_filter"])
+
+
+def test_render_batch_recovers_from_a_too_small_capacity_estimate(dev):
+    cfg, sc, _ = Hh.scene_on("T1", dev)
+    bg = torch.zeros(3, device=dev)
+    pc = SyntheticGaussians(sc)
+    cams = [make_camera(cfg, v, device=dev) for v in range(3)]
+    key = (dev.index, cfg.P, cfg.width, cfg.height)
+    with torch.no_grad():
+        render_batch(cams, pc, PipelineParams(), bg)
+        _C._capacity_hint[key] = 64                                        # far too small: every view overflows
+        o0 = _C.overflow_count
+        res = render_batch(cams, pc, PipelineParams(), bg)
+        assert _C.overflow_count - o0 == 3
+    for v, cam in enumerate(cams):
+        single = render(cam, pc, PipelineParams(), bg)
+        assert torch.equal(res["render"][v], single["render"])
+    assert _C._capacity_hint[key] >= max(res["num_rendered"])
+
+
+def test_capacity_hint_is_a_running_maximum(dev):
+    """A loop that alternates small and large views must not overflow on every large one."""
+    cfg, sc, _ = Hh.scene_on("T1", dev)
+    bg = torch.zeros(3, device=dev)
+    small = {k: (v[:2000].contiguous() if v.shape[0] == cfg.P else v) for k, v in sc.items()}
+    cam = make_camera(cfg, 0, device=dev)
+    far = make_camera(cfg, 0, device=dev)
+    _C._capacity_hint.clear()
+    a_big = Hh.fwd_args(cfg, sc, cam, bg)
+    big = _C.rasterize_gaussians(*a_big)[0]
+    o0 = _C.overflow_count
+    # same shape key (P, W, H), much smaller view: shrink the scales so few tiles are touched
+    sc_small = dict(sc); sc_small["scales"] = sc["scales"] * 0.05
+    for _ in range(3):
+        n_small = _C.rasterize_gaussians(*Hh.fwd_args(cfg, sc_small, cam, bg))[0]
+        n_big = _C.rasterize_gaussians(*a_big)[0]
+    assert n_small < 0.7 * big and n_big == big
+    assert _C.overflow_count == o0
+    del small, far
+
+
 # ------------------------------------------------------------------ rasterizer2 extra channels
 def _idxmap_ours(cfg, sc, cam, dev):
     return _C.get_idxmap2(torch.zeros(3, device=dev), sc["means3D"], sc["normal"], sc["scales"], sc["rotations"],
