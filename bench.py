@@ -236,7 +236,8 @@ def run_ours(args, rank, local_rank, world, dev):
             # the collective is one kernel of libb200splat.so over NVLink peer memory; the backward writes its
             # gradients straight into the peer-mapped buffers (no staging copy, no NCCL call in the step)
             try:
-                reducer = parallel.PeerGradientAllReduce(w.P, 16, dev, ctas=args.peer_ctas, multimem=args.multimem,
+                reducer = parallel.PeerGradientAllReduce(w.P, 16, dev, ctas=args.peer_ctas,
+                                                         multimem=(True if args.multimem else False if args.exact_collective else None),
                                                          factored=not args.dense_collective,
                                                          gather_push=not args.gather_pull,
                                                          priority=0 if args.compute_priority else -1)
@@ -935,6 +936,9 @@ def main():
                     help="peer collective: use the view's radii to skip all-zero dL/dSH rows (exact; fewer NVLink "
                          "bytes but fewer loads in flight per CTA — slower at 2 GPUs, see DESIGN.md §7)")
     ap.add_argument("--multimem", action="store_true", help="peer collective: NVSwitch multimem.ld_reduce/st")
+    ap.add_argument("--exact-collective", action="store_true",
+                    help="peer collective: always the rank-order two-shot sum over peer loads (bit-identical to a "
+                         "fixed-order sum); default: in-switch multimem sum of the dense part with 4+ ranks")
     ap.add_argument("--dense-collective", action="store_true",
                     help="peer collective: reduce the materialised 48-float dL/dsh rows (round-1 behaviour) instead of "
                          "the factored SH gradient")

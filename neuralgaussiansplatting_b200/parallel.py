@@ -317,8 +317,8 @@ class PeerGradientAllReduce:
     AUTO_CTAS_FACTORED = {2: 16, 3: 16, 4: 16}     # default 16: the payload is 2.5x smaller but latency-bound
 
     def __init__(self, P: int, sh_coeffs: int = 16, device=None, group=None, n_buffers: int = 2, ctas: int = 0,
-                 multimem: bool = False, backend: str = "auto", factored: bool = True, gather_push: bool = True,
-                 priority: int = 0):
+                 multimem: Optional[bool] = None, backend: str = "auto", factored: bool = True,
+                 gather_push: bool = True, priority: int = 0):
         from . import _lib
         self._libmod = _lib
         self._lib = _lib.load()
@@ -338,7 +338,8 @@ class PeerGradientAllReduce:
         self.slot_floats = -(-(3 * int(P) + 4) // 64) * 64
         self.gather_floats_total = self.world * self.slot_floats if self.factored else 0
         self.n_buffers = int(n_buffers)
-        self.ctas = int(ctas) if ctas and ctas > 0 else (
+        self._ctas_arg = int(ctas) if ctas and ctas > 0 else 0
+        self.ctas = self._ctas_arg if self._ctas_arg else (
             self.AUTO_CTAS_FACTORED.get(self.world, 16) if factored else self.AUTO_CTAS.get(self.world, 8))
         self.flag_bytes = -(-int(self._lib.b200s_peer_allreduce_flag_bytes(self.ctas, self.world)) // 256) * 256
         self.buf_bytes = (self.n_floats + self.gather_floats_total) * 4
@@ -350,6 +351,15 @@ class PeerGradientAllReduce:
         self.mem.local.zero_()
         torch.cuda.synchronize(self.device)
         dist.barrier(group=group)                      # nobody raises a flag before every flag array is zero
+        # multimem=None (auto): with 4+ ranks on an NVSwitch box the 11 dense floats are summed IN the switch
+        # (multimem.ld_reduce) by 4 CTAs — the in-flight step is bound by the SM slots the collective takes from the
+        # rasterizer, not by NVLink (measured at 4 GPUs: 1.98-2.04 ms/step vs 2.07-2.08 for the peer-load sum;
+        # 8 GPUs: see DESIGN.md §7). The switch's summation order is its own: every replica receives identical
+        # bits, equal to the rank-order sum to rounding. multimem=False keeps the exact rank-order two-shot sum.
+        if multimem is None:
+            multimem = self.factored and self.world >= 4 and self.mem.multicast_ptr != 0
+            if multimem and not self._ctas_arg:
+                self.ctas = 4
         self.multimem = bool(multimem) and self.mem.multicast_ptr != 0
         # factored mode: push the factor slots through the NVSwitch multicast mapping (multimem.st, an exact copy)
         # when the box has one; otherwise every rank pulls the foreign slots with peer loads

@@ -11,11 +11,6 @@ try:
 except Exception as e: print("$name parse failed", e)
 PY
 }
-run pull16_a 29701 --gather-pull
-run pull16_b 29702 --gather-pull
-run push16 29703
-run mmpush4 29704 --multimem --peer-ctas 4
-run mmpush8 29705 --multimem --peer-ctas 8
-run mmpull8 29706 --multimem --peer-ctas 8 --gather-pull
-run pull16_block 29707 --gather-pull --allreduce blocking
-run pull16_chigh 29708 --gather-pull --collective-high-priority
+run default 29701
+run mm2 29702 --peer-ctas 2
+run exact6 29703 --exact-collective --peer-ctas 6
