@@ -352,14 +352,14 @@ class PeerGradientAllReduce:
         torch.cuda.synchronize(self.device)
         dist.barrier(group=group)                      # nobody raises a flag before every flag array is zero
         # multimem=None (auto): with 4+ ranks on an NVSwitch box the 11 dense floats are summed IN the switch
-        # (multimem.ld_reduce) by 4 CTAs — the in-flight step is bound by the SM slots the collective takes from the
-        # rasterizer, not by NVLink (measured at 4 GPUs: 1.98-2.04 ms/step vs 2.07-2.08 for the peer-load sum;
-        # 8 GPUs: see DESIGN.md §7). The switch's summation order is its own: every replica receives identical
+        # (multimem.ld_reduce) by TWO CTAs — the overlapped step is bound by the SM slots the collective takes from
+        # the rasterizer, not by NVLink (measured, ms/step: 4 GPUs 2.00 vs 2.07-2.08 for the peer-load sum; 8 GPUs
+        # 2.15 with 2 CTAs, 2.30 with 4, 2.32 for the peer-load sum with 6; one GPU 1.89 — DESIGN.md §7). The switch's summation order is its own: every replica receives identical
         # bits, equal to the rank-order sum to rounding. multimem=False keeps the exact rank-order two-shot sum.
         if multimem is None:
             multimem = self.factored and self.world >= 4 and self.mem.multicast_ptr != 0
             if multimem and not self._ctas_arg:
-                self.ctas = 4
+                self.ctas = 2
         self.multimem = bool(multimem) and self.mem.multicast_ptr != 0
         # factored mode: push the factor slots through the NVSwitch multicast mapping (multimem.st, an exact copy)
         # when the box has one; otherwise every rank pulls the foreign slots with peer loads
