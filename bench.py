@@ -390,6 +390,8 @@ def run_ours(args, rank, local_rank, world, dev):
         out["full_iteration"] = full_iteration_ours(args, w, _C, dev)
     if rank == 0:
         out.update(roofline_pass(args, w, lib, _C, lambda s: step_resident(s, collective=False)))
+        if world == 1 and args.blend_mode == "strict":
+            out["fast_mode"] = fast_mode_block(args, w, lib, _C, step_resident, dev)
         if not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(w)
     if not args.no_render_only:
@@ -399,6 +401,57 @@ def run_ours(args, rank, local_rank, world, dev):
         if rank == 0:
             out["render_only"] = ro
     return out
+
+
+def fast_mode_block(args, w, lib, _C, step_resident, dev):
+    """"perf is reported in both". The same K steps with blend_mode = 1 (ex2.approx falloff in
+    both blend kernels), its two blend stage times, and its deviation from strict mode on view 0 (image max-abs,
+    n_contrib mismatches, gradient relative L2). The headline `value` stays strict mode."""
+    import ctypes as C
+    from neuralgaussiansplatting_b200 import _lib
+    v = w.view_of(0)
+    fa = w.fwd_args(v)
+
+    def fwd_bwd():
+        o = _C.forward_with_state(*fa, names=["n_contrib"])
+        (R, color, radii, geom, binning, img), st = o
+        g = _C.rasterize_gaussians_backward(fa[0], fa[1], radii, fa[2], fa[4], fa[5], fa[6], fa[7], fa[8], fa[9],
+                                            fa[10], fa[11], w.dL[v], fa[14], fa[15], fa[16], geom, R, binning, img, False)
+        return color, st["n_contrib"], g
+
+    c0, n0, g0 = fwd_bwd()
+    try:
+        _C.config["blend_mode"] = 1
+        c1, n1, g1 = fwd_bwd()
+        for s in range(3):
+            step_resident(s, collective=False)
+        ms = timed_region(lambda s: step_resident(s, collective=False), args.steps, 1, dev)
+        saved = w.view_of
+        w.view_of = lambda s: v
+        try:
+            lib.b200s_profile_begin()
+            for s in range(args.steps):
+                step_resident(s, collective=False)
+            st_ms = (C.c_float * len(_lib.STAGES))()
+            st_calls = (C.c_int32 * len(_lib.STAGES))()
+            _lib.check(lib.b200s_profile_end(st_ms, st_calls), "b200s_profile_end")
+        finally:
+            w.view_of = saved
+    finally:
+        _C.config["blend_mode"] = 0
+
+    def rel(a, b):
+        return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-300))
+
+    i_f, i_b = _lib.STAGES.index("blend_fwd"), _lib.STAGES.index("blend_bwd")
+    names = ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")
+    return {"what": BLEND_MODES[1], "value": round(args.steps / (ms * 1e-3), 3), "unit": UNIT,
+            "ms_per_step": round(ms / args.steps, 4),
+            "blend_fwd_ms": round(st_ms[i_f] / args.steps, 5), "blend_bwd_ms": round(st_ms[i_b] / args.steps, 5),
+            "vs_strict": {"image_max_abs": float((c1 - c0).abs().max()),
+                          "n_contrib_mismatch_pixels": int((n0 != n1).sum()), "pixels": int(n0.numel()),
+                          "grad_rel_l2": {k: round(rel(g1[i], g0[i]), 9) for i, k in enumerate(names)
+                                          if g0[i] is not None and k in ("means3D", "opacity", "sh", "scales", "rotations")}}}
 
 
 BLEND_MODES = {0: "strict (expf, bit-exact n_contrib)", 1: "fast (ex2.approx falloff, forward and backward)"}

@@ -94,7 +94,10 @@ typedef struct B200sForwardArgs {
     void* img_ws;   size_t img_bytes;       /* >= b200s_image_workspace_size(W,H) */
     void* bin_ws;   size_t bin_bytes;       /* >= b200s_binning_workspace_size(capacity,W,H) */
     int64_t bin_capacity;                   /* instances the binning workspace can hold */
-    int32_t blend_mode;      /* 0 = strict (expf, bit-exact n_contrib); 1 = fast (ex2.approx) */
+    int32_t blend_mode;      /* 0 = strict (expf as the reference, bit-exact n_contrib — the parity gate);
+                              * 1 = fast: falloff as ex2.approx(power*log2 e) on a pre-scaled conic; image within 1e-5,
+                              *     n_contrib may differ on isolated threshold pixels. b200s_backward must be called
+                              *     with the same blend_mode as the forward whose state it consumes. */
     int32_t reserved;
 } B200sForwardArgs;
 

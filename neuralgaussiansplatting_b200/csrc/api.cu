@@ -117,6 +117,7 @@ int check_forward_args(const B200sForwardArgs* a) {
     if (has_sr == (a->cov3D_precomp != nullptr)) return B200S_E_BADARG;
     if (a->shs && a->M <= 0) return B200S_E_BADARG;
     if (a->W > 65535 * TILE || a->H > 65535 * TILE) return B200S_E_UNSUPPORTED;
+    if (a->blend_mode != 0 && a->blend_mode != 1) return B200S_E_BADARG;
     if (a->P >= (1 << 30)) return B200S_E_UNSUPPORTED;   // packed look-back word of scan_compact
     if (!a->geom_ws || !a->img_ws) return B200S_E_BADARG;
     if (a->geom_bytes < b200s_geometry_workspace_size(a->P)) return B200S_E_WORKSPACE;
@@ -239,6 +240,7 @@ int b200s_forward_render(const B200sForwardArgs* a, b200s_stream_t stream_) {
     b.ranges = im.ranges; b.point_list = bw.vals[final_buf]; b.rec = g.rec;
     b.background = a->background;
     b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last; b.out_color = a->out_color;
+    b.fast = a->blend_mode == 1;
     {
         ProfScope ps(B200S_STAGE_BLEND_FWD, stream);
         rc = launch_blend_fwd(b, blend_fwd_warps(d.tiles), stream);
@@ -320,6 +322,7 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
         b.point_offsets = g.point_offsets;
         b.background = a->background; b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last;
         b.dL_dpix = a->dL_dout_color; b.accum = ws.accum; b.partial = ws.partial; b.deterministic = a->deterministic;
+        b.fast = a->blend_mode == 1;
         int rc;
         {
             ProfScope ps(B200S_STAGE_BLEND_BWD, stream);
@@ -458,7 +461,7 @@ extern "C" int b200s_count_pairs(const B200sForwardArgs* a, unsigned long long* 
     b.W = a->W; b.H = a->H; b.grid_x = d.gx; b.grid_y = d.gy;
     b.ranges = im.ranges; b.point_list = bw.vals[sort_num_passes(d.tiles) & 1]; b.rec = g.rec;
     b.background = a->background; b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last;
-    b.out_color = a->out_color;
+    b.out_color = a->out_color; b.fast = 0;
     return launch_count_pairs(b, counts_dev, stream);
 }
 

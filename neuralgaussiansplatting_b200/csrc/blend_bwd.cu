@@ -68,7 +68,7 @@ __device__ __forceinline__ float reduce9(float (&acc)[9], int lane, int& which) 
     return r;
 }
 
-template <int NW, int SPT>
+template <int NW, int SPT, bool FAST>
 __global__ void __launch_bounds__(32 * NW, bwd_min_blocks(NW))
 blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
     using WB = WarpBlocks<NW>;
@@ -260,16 +260,21 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
                 const float4 Q = s_q2[buf][idx];
                 const uint32_t lpos = __float_as_uint(Q.z);
                 float dx[NX], ax[NX], bx[NX], dy[NY], cy[NY];
+                // FAST (blend_mode 1): the forward's ex2.approx evaluation, conic pre-scaled into log2 units
+                const float kA = FAST ? A.z * (-0.5f * LOG2E_F) : A.z;
+                const float kB = FAST ? A.w * (-LOG2E_F) : A.w;
+                const float kC = FAST ? B.x * (-0.5f * LOG2E_F) : B.x;
+                const float thrq = FAST ? Q.y * LOG2E_F : Q.y;
 #pragma unroll
                 for (int i = 0; i < NX; ++i) {
                     dx[i] = fsub(A.x, pxf[i]);
-                    ax[i] = fmul(dx[i], A.z);
-                    bx[i] = fmul(dx[i], A.w);
+                    ax[i] = fmul(dx[i], kA);
+                    bx[i] = fmul(dx[i], kB);
                 }
 #pragma unroll
                 for (int i = 0; i < NY; ++i) {
                     dy[i] = fsub(A.y, pyf[i]);
-                    cy[i] = fmul(dy[i], fmul(dy[i], B.x));
+                    cy[i] = fmul(dy[i], fmul(dy[i], kC));
                 }
                 float acc[9];
 #pragma unroll
@@ -279,14 +284,19 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
                 for (int s = 0; s < PX; ++s) {
                     if (!((bj >> s) & 1u)) continue;          // warp-uniform
                     const int ix = s % NX, iy = s / NX;
-                    const float sq = ffma(dx[ix], ax[ix], cy[iy]);
-                    const float power = ffma(sq, -0.5f, -fmul(dy[iy], bx[ix]));
+                    float power;
+                    if (FAST) {
+                        power = fmaf(dy[iy], bx[ix], fmaf(dx[ix], ax[ix], cy[iy]));      // log2 units
+                    } else {
+                        const float sq = ffma(dx[ix], ax[ix], cy[iy]);
+                        power = ffma(sq, -0.5f, -fmul(dy[iy], bx[ix]));
+                    }
                     if (lpos >= lastc[s]) continue;          // behind this pixel's last contributor
-                    if (power > 0.0f || power < Q.y) continue;
+                    if (power > 0.0f || power < thrq) continue;
                     // Same accurate expf as the forward: T is recovered by dividing by (1 - alpha), which
                     // amplifies any mismatch with the forward's alpha by alpha / (1 - alpha) (up to 99x), so a
                     // MUFU.EX2-only G (2^-22 relative error) costs 2.4e-4 rel-L2 on dL/dopacity (measured, C1).
-                    const float G = expf(power);
+                    const float G = FAST ? ex2_approx(power) : expf(power);
                     const float alpha = fminf(0.99f, fmul(B.y, G));
                     if (alpha < ALPHA_MIN_B) continue;
                     any = true;
@@ -337,7 +347,8 @@ template <int NW>
 static int launch_blend_bwd_nw(const BlendBwdParams& p, cudaStream_t stream) {
     const int tiles = p.grid_x * p.grid_y;
     count_launch();
-    blend_bwd_kernel<NW, (NW >= 8 ? 1 : BLEND_SPT)><<<tiles, 32 * NW, 0, stream>>>(p);
+    if (p.fast) blend_bwd_kernel<NW, (NW >= 8 ? 1 : BLEND_SPT), true><<<tiles, 32 * NW, 0, stream>>>(p);
+    else blend_bwd_kernel<NW, (NW >= 8 ? 1 : BLEND_SPT), false><<<tiles, 32 * NW, 0, stream>>>(p);
     return (int)cudaGetLastError();
 }
 

@@ -23,7 +23,11 @@ namespace b200s {
 
 constexpr float ALPHA_MIN = BLEND_ALPHA_MIN;
 
-template <int NW, int SPT>
+// FAST (blend_mode 1): the falloff exp(power) is evaluated as ex2.approx(power * log2 e) with the conic pre-scaled by
+// -0.5*log2(e) / -log2(e) once per staged Gaussian, and the quadratic form is left to FMA contraction (2 instead of 3
+// instructions per pixel, 2 instead of ~9 for the exponential). Not bit-exact: alpha differs from expf's by ~1e-7
+// relative, so n_contrib can differ on isolated threshold pixels; the backward uses the same evaluation.
+template <int NW, int SPT, bool FAST>
 __global__ void __launch_bounds__(32 * NW, fwd_min_blocks(NW))
 blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     using WB = WarpBlocks<NW>;
@@ -209,26 +213,35 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
                 const float4 B = s_q1[buf][idx];
                 const float4 Q = s_q2[buf][idx];
                 float dx[NX], ax[NX], bx[NX], dy[NY], cy[NY];
+                const float kA = FAST ? A.z * (-0.5f * LOG2E_F) : A.z;
+                const float kB = FAST ? A.w * (-LOG2E_F) : A.w;
+                const float kC = FAST ? B.x * (-0.5f * LOG2E_F) : B.x;
+                const float thrq = FAST ? Q.y * LOG2E_F : Q.y;
 #pragma unroll
                 for (int i = 0; i < NX; ++i) {
                     dx[i] = fsub(A.x, pxf[i]);
-                    ax[i] = fmul(dx[i], A.z);
-                    bx[i] = fmul(dx[i], A.w);
+                    ax[i] = fmul(dx[i], kA);
+                    bx[i] = fmul(dx[i], kB);
                 }
 #pragma unroll
                 for (int i = 0; i < NY; ++i) {
                     dy[i] = fsub(A.y, pyf[i]);
-                    cy[i] = fmul(dy[i], fmul(dy[i], B.x));
+                    cy[i] = fmul(dy[i], fmul(dy[i], kC));
                 }
 #pragma unroll
                 for (int s = 0; s < PX; ++s) {
                     if (!((bj >> s) & 1u)) continue;          // warp-uniform
                     const int ix = s % NX, iy = s / NX;
-                    const float sq = ffma(dx[ix], ax[ix], cy[iy]);
-                    const float power = ffma(sq, -0.5f, -fmul(dy[iy], bx[ix]));
+                    float power;
+                    if (FAST) {
+                        power = fmaf(dy[iy], bx[ix], fmaf(dx[ix], ax[ix], cy[iy]));      // log2 units
+                    } else {
+                        const float sq = ffma(dx[ix], ax[ix], cy[iy]);
+                        power = ffma(sq, -0.5f, -fmul(dy[iy], bx[ix]));
+                    }
                     if ((done >> s) & 1u) continue;
-                    if (power > 0.0f || power < Q.y) continue;
-                    const float alpha = fminf(0.99f, fmul(B.y, expf(power)));
+                    if (power > 0.0f || power < thrq) continue;
+                    const float alpha = fminf(0.99f, fmul(B.y, FAST ? ex2_approx(power) : expf(power)));
                     if (alpha < ALPHA_MIN) continue;
                     const float test_T = fmul(T[s], fsub(1.0f, alpha));
                     if (test_T < 0.0001f) { done |= 1u << s; continue; }
@@ -315,7 +328,8 @@ template <int NW>
 static int launch_blend_fwd_nw(const BlendFwdParams& p, cudaStream_t stream) {
     const int tiles = p.grid_x * p.grid_y;
     count_launch();
-    blend_fwd_kernel<NW, (NW >= 8 ? 1 : BLEND_SPT)><<<tiles, 32 * NW, 0, stream>>>(p);
+    if (p.fast) blend_fwd_kernel<NW, (NW >= 8 ? 1 : BLEND_SPT), true><<<tiles, 32 * NW, 0, stream>>>(p);
+    else blend_fwd_kernel<NW, (NW >= 8 ? 1 : BLEND_SPT), false><<<tiles, 32 * NW, 0, stream>>>(p);
     return (int)cudaGetLastError();
 }
 

@@ -38,6 +38,7 @@ struct BlendFwdParams {
     uint32_t* n_contrib;
     uint32_t* tile_last;
     float* out_color;
+    int fast;          // blend_mode 1: ex2.approx falloff
 };
 
 struct BlendBwdParams {
@@ -54,6 +55,7 @@ struct BlendBwdParams {
     float* accum;      // [P][ACC_STRIDE] atomic mode
     float* partial;    // [R][ACC_STRIDE] deterministic mode
     int deterministic;
+    int fast;          // blend_mode 1: must match the forward that produced the state
 };
 
 struct PreprocessBwdParams {
