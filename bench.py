@@ -588,24 +588,27 @@ def full_iteration_reference(args, w, ref, kw_of, BK, dev):
 
 
 def ncu_traffic(stage):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernel, from the newest committed
-    `ncu --set full` summary under profiles/ (captured on the C3 workload by tools/_round.sh); None if absent."""
+    """(dram__bytes_read.sum + dram__bytes_write.sum, smsp__inst_executed.sum, source) per launch of the stage's
+    kernel, from the newest committed `ncu --set full` summary under profiles/ (captured on the C3 workload by
+    tools/_round.sh); Nones if absent."""
     import csv
     files = sorted((ROOT / "profiles").glob("r*_ncu_full_summary_C3.csv"))
     if not files:
-        return None, None
+        return None, None, None
     rows = list(csv.reader(open(files[-1])))
     hdr, units = rows[0], rows[1]
     try:
         ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
     except ValueError:
-        return None, None
+        return None, None, None
+    ii = hdr.index("smsp__inst_executed.sum") if "smsp__inst_executed.sum" in hdr else None
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     for r in rows[2:]:
         if f"{stage}_kernel" in r[0]:
             b = float(r[ir]) * scale.get(units[ir], 1.0) + float(r[iw]) * scale.get(units[iw], 1.0)
-            return int(b), f"profiles/{files[-1].name} (ncu --set full, one launch, view 0)"
-    return None, None
+            inst = int(float(r[ii])) if ii is not None else None
+            return int(b), inst, f"profiles/{files[-1].name} (ncu --set full, one launch, view 0)"
+    return None, None, None
 
 
 def roofline_pass(args, w, lib, _C, step_fn):
@@ -614,7 +617,8 @@ def roofline_pass(args, w, lib, _C, step_fn):
     from neuralgaussiansplatting_b200 import _lib
     dev = w.dev
     hbm_peak, peak_src, sm_max = load_peaks()
-    fp32_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12
+    sm_peaks, sm_src = load_sm_peaks(sm_max)
+    fp32_peak = float(sm_peaks["fp32_tflops"])
     v = w.view_of(0)
     saved = w.view_of
     w.view_of = lambda s: v
@@ -640,12 +644,19 @@ def roofline_pass(args, w, lib, _C, step_fn):
     rows = stage_table(w, list(ms), list(calls), args.steps, counts, P_vis, N, hbm_peak, fp32_peak)
     top = max((k for k in rows if "frac" in rows[k]), key=lambda k: rows[k]["ms_per_step"])
     r = rows[top]
-    traffic, traffic_src = ncu_traffic(top)
+    traffic, winst, traffic_src = ncu_traffic(top)
     roof = {"kernel": top, "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
             "frac": r["frac"], "traffic": traffic, "traffic_source": traffic_src, "ms_per_launch": r["ms_per_step"],
-            "peak_source": (peak_src if r["bound"] == "hbm" else
-                            f"nominal FP32 FMA: 148 SM x 128 lanes x 2 x {sm_max:.0f} MHz (no measured FP32 peak)"),
+            "peak_source": peak_src if r["bound"] == "hbm" else f"FP32 FMA rate {sm_src}",
             "share_of_step": round(r["ms_per_step"] / sum(x["ms_per_step"] for x in rows.values()), 4)}
+    if winst and r["bound"] != "hbm":
+        # what actually limits the blend kernels: warp-instruction issue (fp32 `achieved` counts only the reference's
+        # algorithmic flops; the kernel also issues compares, selects, shuffles and shared-memory loads)
+        ach = winst / (r["ms_per_step"] * 1e-3) / 1e9
+        roof["issue"] = {"warp_inst_per_launch": winst, "achieved": round(ach, 1), "peak": sm_peaks["issue_ginst_per_s"],
+                         "unit": "G warp-inst/s", "frac": round(ach / sm_peaks["issue_ginst_per_s"], 4),
+                         "what": "smsp__inst_executed.sum of the committed ncu capture / the live launch time, against "
+                                 f"the issue-slot peak {sm_src}"}
     return {"roofline": roof, "stages": rows,
             "workload_counts": {"P": w.P, "P_visible": P_vis, "num_rendered": N, "pairs_traversed_fwd": counts[0],
                                 "pairs_contributing": counts[1], "pairs_traversed_bwd": counts[2]}}

@@ -9,6 +9,9 @@
 #include <mutex>
 #include <vector>
 #include "kernels.cuh"
+#if defined(B200S_NVTX) && B200S_NVTX
+#include <nvtx3/nvToolsExt.h>
+#endif
 
 using namespace b200s;
 
@@ -47,6 +50,13 @@ void prof_end(int stage, cudaStream_t stream) {
     cudaEventRecord(e1, stream);
     g_brackets.push_back({stage, e0, e1});
 }
+#if defined(B200S_NVTX) && B200S_NVTX
+static const char* const kStageNames[B200S_NUM_STAGES] = {
+    "b200s:preprocess", "b200s:scan", "b200s:expand", "b200s:sort", "b200s:ranges", "b200s:blend_fwd",
+    "b200s:blend_bwd", "b200s:preprocess_bwd", "b200s:idxmap", "b200s:idxmap_bwd", "b200s:misc"};
+void nvtx_push(int stage) { nvtxRangePushA(stage >= 0 && stage < B200S_NUM_STAGES ? kStageNames[stage] : "b200s:?"); }
+void nvtx_pop() { nvtxRangePop(); }
+#endif
 }  // namespace b200s
 
 extern "C" int b200s_profile_begin(void) {

@@ -92,10 +92,22 @@ struct PreprocessBwdParams {
 void prof_begin(int stage, cudaStream_t stream);
 void prof_end(int stage, cudaStream_t stream);
 void count_launch(int n = 1);
+// Built with -DB200S_NVTX=1 (python -m neuralgaussiansplatting_b200.build --tag nvtx -DB200S_NVTX=1) every stage
+// bracket also opens an NVTX range named after the stage, so an nsys / ncu --nvtx timeline shows K1..K16 by name.
+// Off by default: the product library carries no NVTX calls.
+#if defined(B200S_NVTX) && B200S_NVTX
+void nvtx_push(int stage);
+void nvtx_pop();
+#else
+static inline void nvtx_push(int) {}
+static inline void nvtx_pop() {}
+#endif
 struct ProfScope {
     int stage; cudaStream_t stream;
-    ProfScope(int st, cudaStream_t s) : stage(st), stream(s) { prof_begin(stage, stream); }
-    ~ProfScope() { prof_end(stage, stream); }
+    ProfScope(int st, cudaStream_t s) : stage(st), stream(s) { nvtx_push(stage); prof_begin(stage, stream); }
+    ~ProfScope() { prof_end(stage, stream); nvtx_pop(); }
+    ProfScope(const ProfScope&) = delete;
+    ProfScope& operator=(const ProfScope&) = delete;
 };
 int launch_count_pairs(const BlendFwdParams& p, unsigned long long* counts, cudaStream_t stream);
 

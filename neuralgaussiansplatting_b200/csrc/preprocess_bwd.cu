@@ -41,14 +41,8 @@ __device__ __forceinline__ float dot(float3 a, float3 b) { return a.x * b.x + a.
 template <typename Get, typename Put>
 __device__ __forceinline__ float3 sh_backward(int deg, float x, float y, float z, float3 dRGB, Get get, Put put) {
     float3 dx = f3(0, 0, 0), dy = f3(0, 0, 0), dz = f3(0, 0, 0);
-    // dL/dsh[k] = basis_k * dL/dRGB: single-rounding products of the shared basis (sh_grad.cuh), which the
-    // factored-gradient reconstruction reproduces bit for bit
-    float bas[16];
-    sh_basis(deg, x, y, z, bas);
-    const int ncoef = (deg + 1) * (deg + 1);
-#pragma unroll
-    for (int k = 0; k < 16; ++k)
-        if (k < ncoef) put(k, f3(fmul(bas[k], dRGB.x), fmul(bas[k], dRGB.y), fmul(bas[k], dRGB.z)));
+    // the coefficients are consumed first (get) and dL/dsh produced last (put), so that put may overwrite the
+    // storage get reads from and the 48 coefficients never have to be live in registers together with the basis
     if (deg > 0) {
         const float3 s1 = get(1), s2 = get(2), s3 = get(3);
         dx = (-bSH_C1) * s3;
@@ -75,6 +69,14 @@ __device__ __forceinline__ float3 sh_backward(int deg, float x, float y, float z
             }
         }
     }
+    // dL/dsh[k] = basis_k * dL/dRGB: single-rounding products of the shared basis (sh_grad.cuh), which the
+    // factored-gradient reconstruction reproduces bit for bit; coefficients above the active degree get zeros
+    float bas[16];
+    sh_basis(deg, x, y, z, bas);
+    const int ncoef = (deg + 1) * (deg + 1);
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        put(k, k < ncoef ? f3(fmul(bas[k], dRGB.x), fmul(bas[k], dRGB.y), fmul(bas[k], dRGB.z)) : f3(0, 0, 0));
     return f3(dot(dx, dRGB), dot(dy, dRGB), dot(dz, dRGB));
 }
 
@@ -280,23 +282,29 @@ preprocess_bwd_kernel(const __grid_constant__ PreprocessBwdParams p) {
             if (vis_mask != 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
             __syncwarp();
             float* row = tile + lane * PB_ROW_PAD;
-            float v[PB_ROW_FLOATS];
-            if (visible) {
-#pragma unroll
-                for (int k = 0; k < 12; ++k) {
-                    const float4 t = reinterpret_cast<const float4*>(row)[k];
-                    v[4 * k] = t.x; v[4 * k + 1] = t.y; v[4 * k + 2] = t.z; v[4 * k + 3] = t.w;
-                }
-            }
-            // the row now lives in registers: reuse its shared-memory slot for dL/dsh
-            if (write_rows) {
+            if (!visible && write_rows) {
 #pragma unroll
                 for (int k = 0; k < 12; ++k) reinterpret_cast<float4*>(row)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
             if (visible) {
+                // the lane's row is read with 16-byte loads (conflict-free at the 52-float pitch), four coefficients
+                // at a time; its shared-memory slot is then reused for dL/dsh
+                float o[PB_ROW_FLOATS];
                 const float3 dd = sh_backward(
-                    p.D, dir.x, dir.y, dir.z, dRGB, [&](int k) { return f3(v[3 * k], v[3 * k + 1], v[3 * k + 2]); },
-                    [&](int k, float3 g) { if (write_rows) { row[3 * k] = g.x; row[3 * k + 1] = g.y; row[3 * k + 2] = g.z; } });
+                    p.D, dir.x, dir.y, dir.z, dRGB,
+                    [&](int k) {
+                        const float4 t0 = reinterpret_cast<const float4*>(row)[(3 * k) >> 2];
+                        const float4 t1 = reinterpret_cast<const float4*>(row)[(3 * k + 2) >> 2];
+                        const int r = (3 * k) & 3;   // offset of the coefficient's first float inside t0
+                        return r == 0 ? f3(t0.x, t0.y, t0.z) : r == 1 ? f3(t0.y, t0.z, t0.w)
+                             : r == 2 ? f3(t0.z, t0.w, t1.x) : f3(t0.w, t1.x, t1.y);
+                    },
+                    [&](int k, float3 g) { o[3 * k] = g.x; o[3 * k + 1] = g.y; o[3 * k + 2] = g.z; });
+                if (write_rows) {
+#pragma unroll
+                    for (int k = 0; k < 12; ++k)
+                        reinterpret_cast<float4*>(row)[k] = make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+                }
                 // dnormvdv (auxiliary.h:107-117)
                 const float3 vv = dir_orig;
                 const float sum2 = vv.x * vv.x + vv.y * vv.y + vv.z * vv.z;

@@ -80,3 +80,45 @@ def test_full_size_invariants(dev, cfg_name):
         ga, gb, gc = (Hh.ours_backward(args, out, d) for d in (a, b, 2.0 * a - 3.0 * b))
         for k in ("means3D", "opacity", "sh", "scales", "rotations"):
             assert Hh.rel_l2(gc[k], 2.0 * ga[k] - 3.0 * gb[k]) < 1e-4, k
+
+
+@pytest.mark.parametrize("cfg_name", ["C3", "C4"])
+def test_full_size_idxmap_against_reference_rasterizer2(dev, cfg_name):
+    """rasterizer2's nearest-point maps (K11..K16) at the full sizes: the 64-bit atomicMin z-buffer against the
+    reference's expand + 63-bit sort + first-of-run (rasterizer_impl.cu:578-615,680-847) — index and depth maps
+    bit-exact, gathered channels equal, encoding within 1e-5; backward equal wherever the reference's racy `+=`
+    (:844-846) is not racing (points hit by exactly one pixel) and conservation of the scattered gradient everywhere."""
+    import math
+    from neuralgaussiansplatting_b200 import _C
+    from neuralgaussiansplatting_b200.synthetic import make_grad_featuremap
+    if not refbind.available("ref_r2"):
+        pytest.skip("oracle/_ref not built")
+    cfg, sc, cam = Hh.scene_on(cfg_name, dev)
+    tx, ty = math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5)
+    n, idx, col, dep, feat = _C.get_idxmap2(
+        torch.zeros(3, device=dev), sc["means3D"], sc["normal"], sc["scales"], sc["rotations"], cam.world_view_transform,
+        cam.full_proj_transform, tx, ty, cfg.height, cfg.width, sc["feature_vector"], sc["shs"], cam.camera_center, False)
+    r2 = refbind.RefR2()
+    R, ridx, rcol, rdep, rfeat, rrad = r2.getidxmap(
+        means3D=sc["means3D"], normal=sc["normal"], scales=sc["scales"], rotations=sc["rotations"],
+        viewmatrix=cam.world_view_transform, projmatrix=cam.full_proj_transform, tan_fovx=tx, tan_fovy=ty,
+        feature_vector=sc["feature_vector"], shs=sc["shs"], campos=cam.camera_center, W=cfg.width, H=cfg.height)
+    assert n == R and n > cfg.width * cfg.height // 4
+    assert torch.equal(idx, ridx)
+    assert torch.equal(dep.view(torch.int32), rdep.view(torch.int32))
+    assert float((col - rcol).abs().max()) < 1e-6
+    assert float((feat[..., :25] - rfeat[..., :25]).abs().max()) < 1e-5
+    assert torch.equal(feat[..., 25:], rfeat[..., 25:])
+    del rcol, rdep, rfeat, rrad, col, dep, feat
+    gf = make_grad_featuremap(cfg, 0, device=dev)
+    (g,) = _C.get_idxmap_backward2(sc["means3D"], cfg.height, cfg.width, cam.camera_center, idx, gf, False)
+    gr = r2.getidxmap_backward(means3D=sc["means3D"], campos=cam.camera_center, out_idx=ridx, grad_feature=gf,
+                               W=cfg.width, H=cfg.height)
+    hits = torch.bincount(idx[idx >= 0].long().flatten(), minlength=cfg.P)
+    once = hits == 1
+    assert int(once.sum()) > 1000 and torch.equal(g[once], gr[once])
+    assert float(g[hits == 0].abs().max()) == 0.0 and float(g[:, :25].abs().max()) == 0.0
+    # conservation: every covered pixel's learned-channel gradient lands on exactly one point
+    want = gf.reshape(-1, 64)[(idx >= 0).flatten()][:, 25:].double().sum(0)
+    assert torch.allclose(g[:, 25:].double().sum(0), want, rtol=1e-6, atol=1e-6)
+    r2.close()
