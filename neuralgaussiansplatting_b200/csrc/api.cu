@@ -251,6 +251,7 @@ int b200s_forward_render(const B200sForwardArgs* a, b200s_stream_t stream_) {
     b.background = a->background;
     b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last; b.out_color = a->out_color;
     b.fast = a->blend_mode == 1;
+    b.P = a->P; b.list_cap = a->bin_capacity;
     {
         ProfScope ps(B200S_STAGE_BLEND_FWD, stream);
         rc = launch_blend_fwd(b, blend_fwd_warps(d.tiles), stream);
@@ -333,6 +334,7 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
         b.background = a->background; b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last;
         b.dL_dpix = a->dL_dout_color; b.accum = ws.accum; b.partial = ws.partial; b.deterministic = a->deterministic;
         b.fast = a->blend_mode == 1;
+        b.P = a->P; b.list_cap = a->num_rendered;
         int rc;
         {
             ProfScope ps(B200S_STAGE_BLEND_BWD, stream);
@@ -472,6 +474,7 @@ extern "C" int b200s_count_pairs(const B200sForwardArgs* a, unsigned long long* 
     b.ranges = im.ranges; b.point_list = bw.vals[sort_num_passes(d.tiles) & 1]; b.rec = g.rec;
     b.background = a->background; b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last;
     b.out_color = a->out_color; b.fast = 0;
+    b.P = a->P; b.list_cap = a->bin_capacity;
     return launch_count_pairs(b, counts_dev, stream);
 }
 

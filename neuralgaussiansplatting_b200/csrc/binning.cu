@@ -408,6 +408,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
     for (int k = 0; k < SORT_ITEMS; ++k) {
         const uint32_t d = dr[k] & 0xffffu;
         const uint32_t pos = s_dstart[d] + wc[d] + (dr[k] >> 16);
+        B200S_CHECK(d <= (uint32_t)SORT_RADIX && pos < (uint32_t)SORT_TILE);
         s_keys[pos] = key[k];
         s_vals[pos] = val[k];
     }
@@ -422,6 +423,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         const uint32_t kk = s_keys[i];
         const uint32_t d = (kk >> shift) & (SORT_RADIX - 1);
         const uint32_t dst = s_gbase[d] + i;
+        B200S_CHECK(dst < n);
         keys_out[dst] = kk;
         vals_out[dst] = s_vals[i];
     }
@@ -563,10 +565,13 @@ expand_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* __restric
             if (o + i < o1) {
                 if (o + i >= end) {
                     ++l;
+                    B200S_CHECK(l < cntj);
                     end = s_end[l]; rwh = s_rwh[l]; rmin = s_rmin[l]; id = s_id[l];
                     w = rwh & 0xffffu; tx = 0; ty = 0;
                 }
                 const uint32_t tile = ((rmin >> 16) + ty) * (uint32_t)grid_x + (rmin & 0xffffu) + tx;
+                B200S_CHECK(w != 0 && ty < (rwh >> 16) && (int64_t)(o + i) < capacity &&
+                            tile < (passes >= 4 ? 0xffffffffu : (1u << (passes * SORT_RADIX_BITS))));
                 tk[i] = tile; tv[i] = id;
                 if (++tx == w) { tx = 0; ++ty; }
                 atomicAdd(&s_hist[tile & (SORT_RADIX - 1)], 1u);

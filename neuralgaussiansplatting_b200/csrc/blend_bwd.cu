@@ -89,6 +89,7 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
     const uint2 range = p.ranges[tile];
     // Entries at list positions >= tile_last contributed to no pixel of the tile.
     const int n = min((int)(range.y - range.x), (int)p.tile_last[tile]);
+    B200S_CHECK(range.x <= range.y && (int64_t)range.y <= p.list_cap);
     if (n <= 0) return;
 
     float pxf[NX], pyf[NY], bx0[NX], by0[NY];
@@ -141,6 +142,7 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
         const int i = k * NT + tid;
         const int pos = n - BATCH + i;
         idc[k] = (pos >= 0) ? (int)list[pos] : -1;
+        B200S_CHECK(idc[k] < p.P);
         if (idc[k] >= 0) {
             const SplatRec* r = p.rec + idc[k];
             cp_async16(&s_q0[0][i], &r->q0);
@@ -227,7 +229,10 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
             }
 #pragma unroll
             for (int k = 0; k < SPT; ++k)
-                if (keep[k]) s_idx[base[k] + __popc(ballot[k] & lt)] = (uint16_t)(k * NT + tid);
+                if (keep[k]) {
+                    B200S_CHECK(base[k] + __popc(ballot[k] & lt) < BATCH);
+                    s_idx[base[k] + __popc(ballot[k] & lt)] = (uint16_t)(k * NT + tid);
+                }
         }
         if (NW == 1) __syncwarp(); else __syncthreads();
 

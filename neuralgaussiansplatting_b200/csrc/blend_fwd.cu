@@ -47,6 +47,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     const int tile_x = tile % p.grid_x, tile_y = tile / p.grid_x;
     const uint2 range = p.ranges[tile];
     const int n = (int)(range.y - range.x);
+    B200S_CHECK(range.x <= range.y && (int64_t)range.y <= p.list_cap);
 
     // pixel ownership: block s = (ix, iy) of this warp, pixel (lane & 7, lane >> 3) inside it
     float pxf[NX], pyf[NY], bx0[NX], by0[NY];
@@ -90,6 +91,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     for (int k = 0; k < SPT; ++k) {
         const int pos = k * NT + tid;
         if (pos < n) {
+            B200S_CHECK(list[pos] < (uint32_t)p.P);
             const SplatRec* r = p.rec + list[pos];
             cp_async16(&s_q0[0][pos], &r->q0);
             cp_async16(&s_q1[0][pos], &r->q1);
@@ -144,6 +146,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
 #pragma unroll
             for (int k = 0; k < SPT; ++k) {
                 if (idn[k] >= 0) {
+                    B200S_CHECK(idn[k] < p.P);
                     const int i = k * NT + tid;
                     const SplatRec* r = p.rec + idn[k];
                     cp_async16(&s_q0[buf ^ 1][i], &r->q0);
@@ -175,7 +178,10 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
             }
 #pragma unroll
             for (int k = 0; k < SPT; ++k)
-                if (keep[k]) s_idx[base[k] + __popc(ballot[k] & lt)] = (uint16_t)(k * NT + tid);
+                if (keep[k]) {
+                    B200S_CHECK(base[k] + __popc(ballot[k] & lt) < BATCH);
+                    s_idx[base[k] + __popc(ballot[k] & lt)] = (uint16_t)(k * NT + tid);
+                }
         }
         if (NW == 1) __syncwarp(); else __syncthreads();
 
@@ -209,6 +215,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
                 m &= m - 1;
                 const uint32_t pk = __shfl_sync(FULL_MASK, packed, j);
                 const uint32_t idx = pk & 0xffffu, bj = pk >> 16;
+                B200S_CHECK(idx < (uint32_t)BATCH && bj < (1u << PX));
                 const float4 A = s_q0[buf][idx];
                 const float4 B = s_q1[buf][idx];
                 const float4 Q = s_q2[buf][idx];
@@ -264,6 +271,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     for (int s = 0; s < PX; ++s) {
         if ((outside >> s) & 1u) continue;
         const size_t pix = (size_t)pix_y[s / NX] * p.W + pix_x[s % NX];
+        B200S_CHECK(pix < plane && last[s] <= (uint32_t)n);
         p.final_T[pix] = T[s];
         p.n_contrib[pix] = last[s];
         p.out_color[pix] = ffma(bg0, T[s], Cr[s]);

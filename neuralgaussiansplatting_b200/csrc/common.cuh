@@ -219,6 +219,23 @@ enum { ERR_LOOKBACK_TIMEOUT = 1u, ERR_PREFILTERED = 2u };
     } while (0)
 
 #ifdef __CUDACC__
+// Checked build (python -m neuralgaussiansplatting_b200.build --tag checked -DB200S_CHECKED=1): every index that is
+// derived from device data (list entries, tile ids, scatter destinations, compaction slots) is range-checked and the
+// kernel traps with a message on the first violation. Stands in for compute-sanitizer, which this pool refuses to
+// run (profiles/r02e_sanitizer_unavailable.txt). The product build compiles the checks out.
+#if defined(B200S_CHECKED) && B200S_CHECKED
+#include <cstdio>
+#define B200S_CHECK(cond)                                                                                   \
+    do {                                                                                                    \
+        if (!(cond)) {                                                                                      \
+            printf("b200s check failed: %s (%s:%d) block %d thread %d\n", #cond, __FILE__, __LINE__,        \
+                   (int)blockIdx.x, (int)threadIdx.x);                                                      \
+            __trap();                                                                                       \
+        }                                                                                                   \
+    } while (0)
+#else
+#define B200S_CHECK(cond) ((void)0)
+#endif
 // ---------------------------------------------------------------------------------
 // Bit-exact geometry. The integer outputs (radii, tiles_touched, depth bits, ranges,
 // n_contrib) are functions of fp32 expression trees whose rounding is fixed by how

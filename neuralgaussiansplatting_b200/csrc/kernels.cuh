@@ -39,6 +39,8 @@ struct BlendFwdParams {
     uint32_t* tile_last;
     float* out_color;
     int fast;          // blend_mode 1: ex2.approx falloff
+    int P;             // checked build only: bounds of point_list entries / of the list itself
+    int64_t list_cap;
 };
 
 struct BlendBwdParams {
@@ -56,6 +58,8 @@ struct BlendBwdParams {
     float* partial;    // [R][ACC_STRIDE] deterministic mode
     int deterministic;
     int fast;          // blend_mode 1: must match the forward that produced the state
+    int P;             // checked build only
+    int64_t list_cap;
 };
 
 struct PreprocessBwdParams {
