@@ -252,6 +252,15 @@ int b200s_forward_render(const B200sForwardArgs* a, b200s_stream_t stream_) {
     b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last; b.out_color = a->out_color;
     b.fast = a->blend_mode == 1;
     b.P = a->P; b.list_cap = a->bin_capacity;
+    b.tile_order = nullptr;
+    // The forward's work per tile is not predicted by its list length (pixels terminate early): measured gain 7 us
+    // for a 9 us ordering kernel at C3, none at C4. Opt-in (B200S_TILE_ORDER=2); the backward's order is exact.
+    if (tile_order_enabled() && tile_order_fwd_enabled()) {
+        ProfScope ps(B200S_STAGE_RANGES, stream);
+        rc = launch_tile_order(im.ranges, nullptr, d.tiles, im.order_fwd, stream);
+        if (rc) return rc;
+        b.tile_order = im.order_fwd;
+    }
     {
         ProfScope ps(B200S_STAGE_BLEND_FWD, stream);
         rc = launch_blend_fwd(b, blend_fwd_warps(d.tiles), stream);
@@ -318,13 +327,15 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
     const int passes = sort_num_passes(d.tiles);
     const int final_buf = passes & 1;
 
+    // zero the raw-sum scratch; the same launch orders the tiles for the backward blend (longest list first)
+    const bool ordered = tile_order_enabled() && a->num_rendered > 0;
     {
         ProfScope misc(B200S_STAGE_MISC, stream);
-        if (a->deterministic) {
-            B200S_CUDA_OK(cudaMemsetAsync(ws.partial, 0, sizeof(float) * ACC_STRIDE * (size_t)(a->num_rendered > 0 ? a->num_rendered : 1), stream));
-        } else {
-            B200S_CUDA_OK(cudaMemsetAsync(ws.accum, 0, sizeof(float) * ACC_STRIDE * (size_t)a->P, stream));
-        }
+        void* zp = a->deterministic ? (void*)ws.partial : (void*)ws.accum;
+        const size_t zb = sizeof(float) * ACC_STRIDE *
+                          (a->deterministic ? (size_t)(a->num_rendered > 0 ? a->num_rendered : 1) : (size_t)a->P);
+        int rc0 = launch_bwd_prologue(zp, zb, im.ranges, im.tile_last, d.tiles, ordered ? im.order_bwd : nullptr, stream);
+        if (rc0) return rc0;
     }
     if (a->num_rendered > 0) {
         BlendBwdParams b;
@@ -335,6 +346,7 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
         b.dL_dpix = a->dL_dout_color; b.accum = ws.accum; b.partial = ws.partial; b.deterministic = a->deterministic;
         b.fast = a->blend_mode == 1;
         b.P = a->P; b.list_cap = a->num_rendered;
+        b.tile_order = ordered ? im.order_bwd : nullptr;
         int rc;
         {
             ProfScope ps(B200S_STAGE_BLEND_BWD, stream);
@@ -475,6 +487,7 @@ extern "C" int b200s_count_pairs(const B200sForwardArgs* a, unsigned long long* 
     b.background = a->background; b.final_T = im.final_T; b.n_contrib = im.n_contrib; b.tile_last = im.tile_last;
     b.out_color = a->out_color; b.fast = 0;
     b.P = a->P; b.list_cap = a->bin_capacity;
+    b.tile_order = nullptr;
     return launch_count_pairs(b, counts_dev, stream);
 }
 

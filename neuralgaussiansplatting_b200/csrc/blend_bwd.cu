@@ -84,7 +84,7 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
     __shared__ int s_cnt[NSEG];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
+    const int tile = p.tile_order ? (int)p.tile_order[blockIdx.x] : (int)blockIdx.x;
     const int tile_x = tile % p.grid_x, tile_y = tile / p.grid_x;
     const uint2 range = p.ranges[tile];
     // Entries at list positions >= tile_last contributed to no pixel of the tile.

@@ -43,7 +43,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     __shared__ int s_cnt[NSEG];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
+    const int tile = p.tile_order ? (int)p.tile_order[blockIdx.x] : (int)blockIdx.x;
     const int tile_x = tile % p.grid_x, tile_y = tile / p.grid_x;
     const uint2 range = p.ranges[tile];
     const int n = (int)(range.y - range.x);

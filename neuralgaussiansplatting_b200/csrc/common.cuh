@@ -108,6 +108,8 @@ struct ImgWS {
     uint32_t* n_contrib;   // [W*H]
     uint2* ranges;         // [tiles]
     uint32_t* tile_last;   // [tiles] max n_contrib over the tile's pixels
+    uint32_t* order_fwd;   // [tiles] tile ids, longest list first (launch order of the forward blend)
+    uint32_t* order_bwd;   // [tiles] same for the backward (list length capped by tile_last)
     size_t bytes;
 };
 
@@ -122,6 +124,8 @@ inline ImgWS carve_img(void* base, int W, int H) {
     s.n_contrib = (uint32_t*)take(4 * px);
     s.ranges = (uint2*)take(8 * tiles);
     s.tile_last = (uint32_t*)take(4 * tiles);
+    s.order_fwd = (uint32_t*)take(4 * tiles);
+    s.order_bwd = (uint32_t*)take(4 * tiles);
     s.bytes = off;
     return s;
 }

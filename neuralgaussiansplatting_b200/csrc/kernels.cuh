@@ -38,6 +38,7 @@ struct BlendFwdParams {
     uint32_t* n_contrib;
     uint32_t* tile_last;
     float* out_color;
+    const uint32_t* tile_order;   // blockIdx.x -> tile id (longest list first) or NULL = identity
     int fast;          // blend_mode 1: ex2.approx falloff
     int P;             // checked build only: bounds of point_list entries / of the list itself
     int64_t list_cap;
@@ -57,6 +58,7 @@ struct BlendBwdParams {
     float* accum;      // [P][ACC_STRIDE] atomic mode
     float* partial;    // [R][ACC_STRIDE] deterministic mode
     int deterministic;
+    const uint32_t* tile_order;   // blockIdx.x -> tile id (longest list first) or NULL = identity
     int fast;          // blend_mode 1: must match the forward that produced the state
     int P;             // checked build only
     int64_t list_cap;
@@ -121,6 +123,11 @@ int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t 
 int sort_num_passes(int tiles);
 int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, int64_t n_hint, int grid_x,
                    int tiles, uint2* ranges, int* final_buf, bool debug, cudaStream_t stream);
+int launch_tile_order(const uint2* ranges, const uint32_t* tile_last, int tiles, uint32_t* order, cudaStream_t stream);
+bool tile_order_enabled();
+bool tile_order_fwd_enabled();
+int launch_bwd_prologue(void* zero, size_t zero_bytes, const uint2* ranges, const uint32_t* tile_last, int tiles,
+                        uint32_t* order, cudaStream_t stream);
 int launch_blend_fwd(const BlendFwdParams& p, int nw, cudaStream_t stream);
 int launch_blend_bwd(const BlendBwdParams& p, int nw, cudaStream_t stream);
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream);
