@@ -444,12 +444,12 @@ constexpr int OUT_ITEMS = 8;
 constexpr int OUT_TILE = EXP_OUT_TILE;                 // 2,048 instances per block
 static_assert(OUT_TILE == EXP_THREADS * OUT_ITEMS, "expansion geometry");
 
-__global__ void __launch_bounds__(EXP_THREADS)
+__global__ void __launch_bounds__(SS_THREADS)
 sorted_scan_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __restrict__ rec,
                    uint32_t* __restrict__ run_end, uint32_t* __restrict__ run_rmin, uint32_t* __restrict__ run_rwh,
                    uint32_t* __restrict__ block_first, B200sHeader* header, int64_t capacity,
                    uint32_t* status, uint32_t* ticket) {
-    __shared__ uint32_t s_warp[EXP_THREADS / 32];
+    __shared__ uint32_t s_warp[SS_THREADS / 32];
     __shared__ uint32_t s_block, s_prefix;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_vis = header->num_visible;
@@ -485,7 +485,7 @@ sorted_scan_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __re
     __syncthreads();
     uint32_t wex = 0, total = 0;
 #pragma unroll
-    for (int w = 0; w < EXP_THREADS / 32; ++w) {
+    for (int w = 0; w < SS_THREADS / 32; ++w) {
         const uint32_t t = s_warp[w];
         if (w < warp) wex += t;
         total += t;
@@ -687,16 +687,26 @@ tile_order_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 }
 
 // Backward prologue: the zero-fill of the raw-sum scratch (the reference's torch::zeros) with block 0 doing the tile
-// ordering meanwhile, so the ordering costs no time of its own (the fill is HBM-bound and takes 4x longer).
+// ordering meanwhile, so the ordering costs no time of its own (the fill is HBM-bound and takes longer). In atomic
+// mode only the rows of visible Gaussians are cleared (radii > 0: the only rows blend_bwd adds to and preprocess_bwd
+// reads): 4 B read per Gaussian + 48 B written per visible one instead of 48 B per Gaussian.
 __global__ void __launch_bounds__(TO_THREADS)
-bwd_prologue_kernel(float4* __restrict__ zero, size_t n16, const uint2* __restrict__ ranges,
-                    const uint32_t* __restrict__ tile_last, int tiles, uint32_t* __restrict__ order) {
+bwd_prologue_kernel(float4* __restrict__ zero, size_t n16, const int* __restrict__ radii, int P,
+                    const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_last, int tiles,
+                    uint32_t* __restrict__ order) {
     if (order != nullptr) {
         if (blockIdx.x == 0) { tile_order_block(ranges, tile_last, tiles, order); return; }
     }
     const size_t first = order != nullptr ? 1 : 0;
     const size_t stride = (size_t)(gridDim.x - first) * TO_THREADS;
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (radii != nullptr) {
+        static_assert(ACC_STRIDE == 12, "three float4 per row");
+        for (size_t i = (size_t)(blockIdx.x - first) * TO_THREADS + threadIdx.x; i < (size_t)P; i += stride) {
+            if (radii[i] > 0) { zero[3 * i] = z; zero[3 * i + 1] = z; zero[3 * i + 2] = z; }
+        }
+        return;
+    }
     for (size_t i = (size_t)(blockIdx.x - first) * TO_THREADS + threadIdx.x; i < n16; i += stride) zero[i] = z;
 }
 
@@ -717,13 +727,14 @@ int launch_tile_order(const uint2* ranges, const uint32_t* tile_last, int tiles,
     return (int)cudaGetLastError();
 }
 
-int launch_bwd_prologue(void* zero, size_t zero_bytes, const uint2* ranges, const uint32_t* tile_last, int tiles,
-                        uint32_t* order, cudaStream_t stream) {
-    // zero_bytes is a multiple of 16 and `zero` 256-byte aligned (workspace carving)
+int launch_bwd_prologue(void* zero, size_t zero_bytes, const int* radii, int P, const uint2* ranges,
+                        const uint32_t* tile_last, int tiles, uint32_t* order, cudaStream_t stream) {
+    // zero_bytes is a multiple of 16 and `zero` 256-byte aligned (workspace carving); radii != NULL: rows of
+    // ACC_STRIDE floats indexed by Gaussian, only the visible ones are cleared
     count_launch();
     const int blocks = 148 * 2 + (order != nullptr ? 1 : 0);
-    bwd_prologue_kernel<<<blocks, TO_THREADS, 0, stream>>>(reinterpret_cast<float4*>(zero), zero_bytes / 16, ranges,
-                                                           tile_last, tiles, order);
+    bwd_prologue_kernel<<<blocks, TO_THREADS, 0, stream>>>(reinterpret_cast<float4*>(zero), zero_bytes / 16, radii, P,
+                                                           ranges, tile_last, tiles, order);
     return (int)cudaGetLastError();
 }
 
@@ -816,7 +827,7 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
         // the depth sort's spare buffers (and its no longer needed sorted keys) hold the runs
         ProfScope ps(B200S_STAGE_EXPAND, stream);
         count_launch(2);
-        sorted_scan_kernel<<<(P + EXP_TILE - 1) / EXP_TILE, EXP_THREADS, 0, stream>>>(
+        sorted_scan_kernel<<<(P + EXP_TILE - 1) / EXP_TILE, SS_THREADS, 0, stream>>>(
             g.vis_ids[0], g.rec, g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, g.header, capacity,
             g.exp_status, g.counters + CTR_EXPAND_TICKET);
         B200S_AFTER_LAUNCH(stream, debug);

@@ -77,9 +77,11 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
     constexpr int BATCH = NT * SPT;
     constexpr int NSEG = NW * SPT;
 
-    __shared__ float4 s_q0[2][BATCH];          // x, y, conic a, conic b
-    __shared__ float4 s_q1[2][BATCH];          // conic c, opacity, r, g
-    __shared__ float4 s_q2[2][BATCH];          // b, power threshold, list pos, destination
+    // staged records, [buffer][field][entry]: field 0 = x, y, conic a, conic b
+    //   field 1 = conic c, opacity, r, g
+    //   field 2 = b, power threshold, list pos, destination
+    // One array, so that the three 16-byte loads of a survivor share one address register (constant offsets).
+    __shared__ float4 s_q[2][3][BATCH];
     __shared__ uint16_t s_idx[BATCH];
     __shared__ int s_cnt[NSEG];
 
@@ -145,9 +147,9 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
         B200S_CHECK(idc[k] < p.P);
         if (idc[k] >= 0) {
             const SplatRec* r = p.rec + idc[k];
-            cp_async16(&s_q0[0][i], &r->q0);
-            cp_async16(&s_q1[0][i], &r->q1);
-            cp_async16(&s_q2[0][i], &r->q2);
+            cp_async16(&s_q[0][0][i], &r->q0);
+            cp_async16(&s_q[0][1][i], &r->q1);
+            cp_async16(&s_q[0][2][i], &r->q2);
         }
     }
     cp_async_commit();
@@ -159,6 +161,7 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
 
     for (int b = 0; b < nb; ++b) {
         const int buf = b & 1;
+        const char* qbase = reinterpret_cast<const char*>(&s_q[buf][0][0]);
         cp_async_wait<0>();
         uint32_t ballot[SPT];
         bool keep[SPT];
@@ -168,14 +171,14 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
             const int pos = n - (b + 1) * BATCH + i;
             keep[k] = false;
             if (pos >= 0) {
-                const float4 q0 = s_q0[buf][i];
-                const float4 q1 = s_q1[buf][i];
+                const float4 q0 = s_q[buf][0][i];
+                const float4 q1 = s_q[buf][1][i];
                 const float thr = power_threshold(q1.y);
                 if (q1.y >= ALPHA_MIN_B) {
                     const ReachCtx rc = make_reach_ctx(q0.x, q0.y, q0.z, q0.w, q1.x, thr, X0, Y0, X1, Y1);
                     keep[k] = rect_reach(rc, X0, Y0, X1, Y1);
                 }
-                float4 q2 = s_q2[buf][i];
+                float4 q2 = s_q[buf][2][i];
                 uint32_t dest = (uint32_t)idc[k];
                 if (p.deterministic) {
                     // slot of this instance in the unsorted (Gaussian-major, tile-minor) order
@@ -186,7 +189,7 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
                 q2.y = thr;
                 q2.z = __uint_as_float((uint32_t)pos);
                 q2.w = __uint_as_float(dest);
-                s_q2[buf][i] = q2;
+                s_q[buf][2][i] = q2;
             }
             ballot[k] = __ballot_sync(FULL_MASK, keep[k]);
             if (lane == 0) s_cnt[k * NW + warp] = __popc(ballot[k]);
@@ -200,9 +203,9 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
                 if (idn[k] >= 0) {
                     const int i = k * NT + tid;
                     const SplatRec* r = p.rec + idn[k];
-                    cp_async16(&s_q0[buf ^ 1][i], &r->q0);
-                    cp_async16(&s_q1[buf ^ 1][i], &r->q1);
-                    cp_async16(&s_q2[buf ^ 1][i], &r->q2);
+                    cp_async16(&s_q[buf ^ 1][0][i], &r->q0);
+                    cp_async16(&s_q[buf ^ 1][1][i], &r->q1);
+                    cp_async16(&s_q[buf ^ 1][2][i], &r->q2);
                 }
             }
         }
@@ -231,7 +234,7 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
             for (int k = 0; k < SPT; ++k)
                 if (keep[k]) {
                     B200S_CHECK(base[k] + __popc(ballot[k] & lt) < BATCH);
-                    s_idx[base[k] + __popc(ballot[k] & lt)] = (uint16_t)(k * NT + tid);
+                    s_idx[base[k] + __popc(ballot[k] & lt)] = (uint16_t)((k * NT + tid) << 4);
                 }
         }
         if (NW == 1) __syncwarp(); else __syncthreads();
@@ -240,10 +243,10 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
             // level 2: lane l tests survivor j0+l against each pixel block of this warp
             uint32_t packed = 0;
             if (j0 + lane < total) {
-                const uint32_t idx = s_idx[j0 + lane];
-                const float4 A = s_q0[buf][idx];
-                const float4 B = s_q1[buf][idx];
-                const float4 Q = s_q2[buf][idx];
+                const uint32_t idx = s_idx[j0 + lane];          // byte offset of the entry (index << 4)
+                const float4 A = *reinterpret_cast<const float4*>(qbase + idx);
+                const float4 B = *reinterpret_cast<const float4*>(qbase + idx + BATCH * 16);
+                const float4 Q = *reinterpret_cast<const float4*>(qbase + idx + 2 * BATCH * 16);
                 const uint32_t lpos = __float_as_uint(Q.z);
                 const ReachCtx rc = make_reach_ctx(A.x, A.y, A.z, A.w, B.x, Q.y, X0, Y0, X1, Y1);
                 uint32_t bits = 0;
@@ -260,9 +263,9 @@ blend_bwd_kernel(const __grid_constant__ BlendBwdParams p) {
                 m &= ~(1u << j);
                 const uint32_t pk = __shfl_sync(FULL_MASK, packed, j);
                 const uint32_t idx = pk & 0xffffu, bj = pk >> 16;
-                const float4 A = s_q0[buf][idx];
-                const float4 B = s_q1[buf][idx];
-                const float4 Q = s_q2[buf][idx];
+                const float4 A = *reinterpret_cast<const float4*>(qbase + idx);
+                const float4 B = *reinterpret_cast<const float4*>(qbase + idx + BATCH * 16);
+                const float4 Q = *reinterpret_cast<const float4*>(qbase + idx + 2 * BATCH * 16);
                 const uint32_t lpos = __float_as_uint(Q.z);
                 float dx[NX], ax[NX], bx[NX], dy[NY], cy[NY];
                 // FAST (blend_mode 1): the forward's ex2.approx evaluation, conic pre-scaled into log2 units

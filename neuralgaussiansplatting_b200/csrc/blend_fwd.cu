@@ -18,6 +18,10 @@
 
 #include "blend_common.cuh"
 
+#ifndef B200S_FWD_BLOCKLISTS
+#define B200S_FWD_BLOCKLISTS 0
+#endif
+
 namespace b200s {
 
 
@@ -36,11 +40,16 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     constexpr int BATCH = NT * SPT;            // list entries staged per round
     constexpr int NSEG = NW * SPT;             // 32-entry segments of a batch, in list order
 
-    __shared__ float4 s_q0[2][BATCH];          // x, y, conic a, conic b
-    __shared__ float4 s_q1[2][BATCH];          // conic c, opacity, r, g
-    __shared__ float4 s_q2[2][BATCH];          // b, power threshold, list pos + 1, -
+    // staged records, [buffer][field][entry]: field 0 = x, y, conic a, conic b
+    //   field 1 = conic c, opacity, r, g
+    //   field 2 = b, power threshold, list pos + 1, -
+    // One array, so that the three 16-byte loads of a survivor share one address register (constant offsets).
+    __shared__ float4 s_q[2][3][BATCH];
     __shared__ uint16_t s_idx[BATCH];          // tile-level survivors of the batch, list order
     __shared__ int s_cnt[NSEG];
+#if B200S_FWD_BLOCKLISTS
+    __shared__ uint8_t s_blk[NW][PX][BATCH];   // per pixel block: entry indices of the survivors that reach it
+#endif
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = p.tile_order ? (int)p.tile_order[blockIdx.x] : (int)blockIdx.x;
@@ -49,29 +58,30 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     const int n = (int)(range.y - range.x);
     B200S_CHECK(range.x <= range.y && (int64_t)range.y <= p.list_cap);
 
-    // pixel ownership: block s = (ix, iy) of this warp, pixel (lane & 7, lane >> 3) inside it
-    float pxf[NX], pyf[NY], bx0[NX], by0[NY];
-    int pix_x[NX], pix_y[NY];
-#pragma unroll
-    for (int i = 0; i < NX; ++i) {
-        const int x0 = tile_x * TILE + WB::col_block(warp, i) * 8;
-        bx0[i] = (float)x0;
-        pix_x[i] = x0 + (lane & 7);
-        pxf[i] = (float)pix_x[i];
-    }
-#pragma unroll
-    for (int i = 0; i < NY; ++i) {
-        const int y0 = tile_y * TILE + WB::row_block(warp, i) * 4;
-        by0[i] = (float)y0;
-        pix_y[i] = y0 + (lane >> 3);
-        pyf[i] = (float)pix_y[i];
-    }
+    // pixel ownership: block s = (ix, iy) of this warp, pixel (lane & 7, lane >> 3) inside it. Only the FLOAT
+    // coordinates stay live across the list loop (the integer ones are re-derived in the epilogue): with both live
+    // the compiler keeps the integers and re-converts them per survivor (3 I2FP per (warp, Gaussian) in the SASS).
+    float pxf[NX], pyf[NY];
     constexpr uint32_t ALL_DONE = (1u << PX) - 1u;
     uint32_t done = 0;
+    {
+        int pix_x[NX], pix_y[NY];
 #pragma unroll
-    for (int s = 0; s < PX; ++s)
-        if (!(pix_x[s % NX] < p.W && pix_y[s / NX] < p.H)) done |= 1u << s;
+        for (int i = 0; i < NX; ++i) {
+            pix_x[i] = tile_x * TILE + WB::col_block(warp, i) * 8 + (lane & 7);
+            pxf[i] = (float)pix_x[i];
+        }
+#pragma unroll
+        for (int i = 0; i < NY; ++i) {
+            pix_y[i] = tile_y * TILE + WB::row_block(warp, i) * 4 + (lane >> 3);
+            pyf[i] = (float)pix_y[i];
+        }
+#pragma unroll
+        for (int s = 0; s < PX; ++s)
+            if (!(pix_x[s % NX] < p.W && pix_y[s / NX] < p.H)) done |= 1u << s;
+    }
     const uint32_t outside = done;
+    const float lane_x = (float)(lane & 7), lane_y = (float)(lane >> 3);
 
     float T[PX], Cr[PX], Cg[PX], Cb[PX];
     uint32_t last[PX];
@@ -93,9 +103,9 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
         if (pos < n) {
             B200S_CHECK(list[pos] < (uint32_t)p.P);
             const SplatRec* r = p.rec + list[pos];
-            cp_async16(&s_q0[0][pos], &r->q0);
-            cp_async16(&s_q1[0][pos], &r->q1);
-            cp_async16(&s_q2[0][pos], &r->q2);
+            cp_async16(&s_q[0][0][pos], &r->q0);
+            cp_async16(&s_q[0][1][pos], &r->q1);
+            cp_async16(&s_q[0][2][pos], &r->q2);
         }
     }
     cp_async_commit();
@@ -107,6 +117,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
 
     for (int b = 0; b < nb; ++b) {
         const int buf = b & 1;
+        const char* qbase = reinterpret_cast<const char*>(&s_q[buf][0][0]);
         cp_async_wait<0>();
         // level 1: every thread tests ITS entries against the tile
         uint32_t ballot[SPT];
@@ -117,17 +128,17 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
             const int pos = b * BATCH + i;
             keep[k] = false;
             if (pos < n) {
-                const float4 q0 = s_q0[buf][i];
-                const float4 q1 = s_q1[buf][i];
+                const float4 q0 = s_q[buf][0][i];
+                const float4 q1 = s_q[buf][1][i];
                 const float thr = power_threshold(q1.y);
                 if (q1.y >= ALPHA_MIN) {
                     const ReachCtx rc = make_reach_ctx(q0.x, q0.y, q0.z, q0.w, q1.x, thr, X0, Y0, X1, Y1);
                     keep[k] = rect_reach(rc, X0, Y0, X1, Y1);
                 }
-                float4 q2 = s_q2[buf][i];
+                float4 q2 = s_q[buf][2][i];
                 q2.y = thr;
                 q2.z = __uint_as_float((uint32_t)(pos + 1));
-                s_q2[buf][i] = q2;
+                s_q[buf][2][i] = q2;
             }
             ballot[k] = __ballot_sync(FULL_MASK, keep[k]);
             if (lane == 0) s_cnt[k * NW + warp] = __popc(ballot[k]);
@@ -149,9 +160,9 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
                     B200S_CHECK(idn[k] < p.P);
                     const int i = k * NT + tid;
                     const SplatRec* r = p.rec + idn[k];
-                    cp_async16(&s_q0[buf ^ 1][i], &r->q0);
-                    cp_async16(&s_q1[buf ^ 1][i], &r->q1);
-                    cp_async16(&s_q2[buf ^ 1][i], &r->q2);
+                    cp_async16(&s_q[buf ^ 1][0][i], &r->q0);
+                    cp_async16(&s_q[buf ^ 1][1][i], &r->q1);
+                    cp_async16(&s_q[buf ^ 1][2][i], &r->q2);
                 }
             }
         }
@@ -180,7 +191,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
             for (int k = 0; k < SPT; ++k)
                 if (keep[k]) {
                     B200S_CHECK(base[k] + __popc(ballot[k] & lt) < BATCH);
-                    s_idx[base[k] + __popc(ballot[k] & lt)] = (uint16_t)(k * NT + tid);
+                    s_idx[base[k] + __popc(ballot[k] & lt)] = (uint16_t)((k * NT + tid) << 4);
                 }
         }
         if (NW == 1) __syncwarp(); else __syncthreads();
@@ -191,19 +202,93 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
         for (int s = 0; s < PX; ++s)
             if (__all_sync(FULL_MASK, (done >> s) & 1u)) blockdone |= 1u << s;
 
+#if B200S_FWD_BLOCKLISTS
+        // level 2 -> one survivor list PER PIXEL BLOCK (list order kept): lane l tests survivor j0+l against each block
+        // of this warp, the hits are compacted per block with a ballot, and every block then walks only its own
+        // list. Against the per-warp walk this drops the 4 uniform block tests, the find-first-set / shuffle
+        // broadcast and the unused row / column factors of every (warp, survivor) visit.
+        int bcnt[PX];
+#pragma unroll
+        for (int s = 0; s < PX; ++s) bcnt[s] = 0;
+        for (int j0 = 0; j0 < total; j0 += 32) {
+            uint32_t bits = 0, ent = 0;
+            if (j0 + lane < total) {
+                const uint32_t idx = s_idx[j0 + lane];          // byte offset of the entry (index << 4)
+                const float4 A = *reinterpret_cast<const float4*>(qbase + idx);
+                const float4 B = *reinterpret_cast<const float4*>(qbase + idx + BATCH * 16);
+                const float thr = reinterpret_cast<const float4*>(qbase + idx + 2 * BATCH * 16)->y;
+                const ReachCtx rc = make_reach_ctx(A.x, A.y, A.z, A.w, B.x, thr, X0, Y0, X1, Y1);
+#pragma unroll
+                for (int s = 0; s < PX; ++s) {
+                    const float rx0 = pxf[s % NX] - lane_x, ry0 = pyf[s / NX] - lane_y;   // exact: small integers
+                    if (rect_reach(rc, rx0, ry0, rx0 + 7.0f, ry0 + 3.0f)) bits |= 1u << s;
+                }
+                bits &= ~blockdone;
+                ent = idx >> 4;
+            }
+#pragma unroll
+            for (int s = 0; s < PX; ++s) {
+                const bool hit = (bits >> s) & 1u;
+                const uint32_t bal = __ballot_sync(FULL_MASK, hit);
+                if (hit) {
+                    B200S_CHECK(bcnt[s] + __popc(bal & lt) < BATCH);
+                    s_blk[warp][s][bcnt[s] + __popc(bal & lt)] = (uint8_t)ent;
+                }
+                bcnt[s] += __popc(bal);
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int s = 0; s < PX; ++s) {
+            const int ix = s % NX, iy = s / NX;
+            const uint8_t* lst = s_blk[warp][s];
+            for (int j = 0; j < bcnt[s]; ++j) {
+                const uint32_t idx = (uint32_t)lst[j] << 4;
+                B200S_CHECK(idx < (uint32_t)BATCH * 16u);
+                const float4 A = *reinterpret_cast<const float4*>(qbase + idx);
+                const float4 B = *reinterpret_cast<const float4*>(qbase + idx + BATCH * 16);
+                const float4 Q = *reinterpret_cast<const float4*>(qbase + idx + 2 * BATCH * 16);
+                const float kA = FAST ? A.z * (-0.5f * LOG2E_F) : A.z;
+                const float kB = FAST ? A.w * (-LOG2E_F) : A.w;
+                const float kC = FAST ? B.x * (-0.5f * LOG2E_F) : B.x;
+                const float thrq = FAST ? Q.y * LOG2E_F : Q.y;
+                const float dx = fsub(A.x, pxf[ix]), dy = fsub(A.y, pyf[iy]);
+                const float ax = fmul(dx, kA), bx = fmul(dx, kB), cy = fmul(dy, fmul(dy, kC));
+                float power;
+                if (FAST) {
+                    power = fmaf(dy, bx, fmaf(dx, ax, cy));      // log2 units
+                } else {
+                    const float sq = ffma(dx, ax, cy);
+                    power = ffma(sq, -0.5f, -fmul(dy, bx));
+                }
+                if ((done >> s) & 1u) continue;
+                if (power > 0.0f || power < thrq) continue;
+                const float alpha = fminf(0.99f, fmul(B.y, FAST ? ex2_approx(power) : expf(power)));
+                if (alpha < ALPHA_MIN) continue;
+                const float test_T = fmul(T[s], fsub(1.0f, alpha));
+                if (test_T < 0.0001f) { done |= 1u << s; continue; }
+                Cr[s] = ffma(T[s], fmul(alpha, B.z), Cr[s]);
+                Cg[s] = ffma(T[s], fmul(alpha, B.w), Cg[s]);
+                Cb[s] = ffma(T[s], fmul(alpha, Q.x), Cb[s]);
+                T[s] = test_T;
+                last[s] = __float_as_uint(Q.z);
+            }
+        }
+        __syncwarp();
+#else
         for (int j0 = 0; j0 < total; j0 += 32) {
             // level 2: lane l tests survivor j0+l against each pixel block of this warp
             uint32_t packed = 0;
             if (j0 + lane < total) {
-                const uint32_t idx = s_idx[j0 + lane];
-                const float4 A = s_q0[buf][idx];
-                const float4 B = s_q1[buf][idx];
-                const float thr = s_q2[buf][idx].y;
+                const uint32_t idx = s_idx[j0 + lane];          // byte offset of the entry (index << 4)
+                const float4 A = *reinterpret_cast<const float4*>(qbase + idx);
+                const float4 B = *reinterpret_cast<const float4*>(qbase + idx + BATCH * 16);
+                const float thr = reinterpret_cast<const float4*>(qbase + idx + 2 * BATCH * 16)->y;
                 const ReachCtx rc = make_reach_ctx(A.x, A.y, A.z, A.w, B.x, thr, X0, Y0, X1, Y1);
                 uint32_t bits = 0;
 #pragma unroll
                 for (int s = 0; s < PX; ++s) {
-                    const float rx0 = bx0[s % NX], ry0 = by0[s / NX];
+                    const float rx0 = pxf[s % NX] - lane_x, ry0 = pyf[s / NX] - lane_y;   // exact: small integers
                     if (rect_reach(rc, rx0, ry0, rx0 + 7.0f, ry0 + 3.0f)) bits |= 1u << s;
                 }
                 bits &= ~blockdone;
@@ -215,10 +300,10 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
                 m &= m - 1;
                 const uint32_t pk = __shfl_sync(FULL_MASK, packed, j);
                 const uint32_t idx = pk & 0xffffu, bj = pk >> 16;
-                B200S_CHECK(idx < (uint32_t)BATCH && bj < (1u << PX));
-                const float4 A = s_q0[buf][idx];
-                const float4 B = s_q1[buf][idx];
-                const float4 Q = s_q2[buf][idx];
+                B200S_CHECK(idx < (uint32_t)BATCH * 16u && (idx & 15u) == 0u && bj < (1u << PX));
+                const float4 A = *reinterpret_cast<const float4*>(qbase + idx);
+                const float4 B = *reinterpret_cast<const float4*>(qbase + idx + BATCH * 16);
+                const float4 Q = *reinterpret_cast<const float4*>(qbase + idx + 2 * BATCH * 16);
                 float dx[NX], ax[NX], bx[NX], dy[NY], cy[NY];
                 const float kA = FAST ? A.z * (-0.5f * LOG2E_F) : A.z;
                 const float kB = FAST ? A.w * (-LOG2E_F) : A.w;
@@ -260,6 +345,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
                 }
             }
         }
+#endif
     }
     cp_async_wait<0>();
 
@@ -270,7 +356,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
 #pragma unroll
     for (int s = 0; s < PX; ++s) {
         if ((outside >> s) & 1u) continue;
-        const size_t pix = (size_t)pix_y[s / NX] * p.W + pix_x[s % NX];
+        const size_t pix = (size_t)__float2int_rn(pyf[s / NX]) * p.W + __float2int_rn(pxf[s % NX]);
         B200S_CHECK(pix < plane && last[s] <= (uint32_t)n);
         p.final_T[pix] = T[s];
         p.n_contrib[pix] = last[s];

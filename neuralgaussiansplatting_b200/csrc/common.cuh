@@ -38,7 +38,18 @@ __host__ __device__ inline size_t align_up(size_t x, size_t a = WS_ALIGN) {
     return (x + a - 1) / a * a;
 }
 
-constexpr int SCAN_THREADS = 256;
+// Threads per block of the look-back scans. All blocks of these small kernels are resident at once, so the look-back
+// of block i walks ~i/32 windows of predecessors before it meets an inclusive word: fewer, larger blocks shorten the
+// chain (B200S_SCAN_THREADS / B200S_SS_THREADS: tuning knobs, A/B'd with build variants). Measured on B200
+// (profiles/r02h_scan_variants.log): sorted_scan 256 -> 1024 threads: expand stage 0.111 -> 0.098 ms at C3, 0.206 ->
+// 0.198 at C4; scan_compact 256 -> 512 / 1024: 0.037 -> 0.040 / 0.043 ms (slower: it is not chain-bound), so it stays.
+#ifndef B200S_SCAN_THREADS
+#define B200S_SCAN_THREADS 256
+#endif
+#ifndef B200S_SS_THREADS
+#define B200S_SS_THREADS 1024
+#endif
+constexpr int SCAN_THREADS = B200S_SCAN_THREADS;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
@@ -53,8 +64,9 @@ constexpr int DEPTH_PASSES = 4;       // onesweep passes over the 32 depth bits
 
 // Expansion geometry: one block turns EXP_TILE depth-sorted Gaussians into their instances.
 constexpr int EXP_THREADS = 256;
+constexpr int SS_THREADS = B200S_SS_THREADS;   // sorted_scan_kernel (the scan in front of the expansion)
 constexpr int EXP_ITEMS = 4;
-constexpr int EXP_TILE = EXP_THREADS * EXP_ITEMS;
+constexpr int EXP_TILE = SS_THREADS * EXP_ITEMS;
 constexpr int EXP_OUT_TILE = EXP_THREADS * 8;   // instances emitted per expansion block
 
 struct GeomWS {

@@ -126,8 +126,8 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
 int launch_tile_order(const uint2* ranges, const uint32_t* tile_last, int tiles, uint32_t* order, cudaStream_t stream);
 bool tile_order_enabled();
 bool tile_order_fwd_enabled();
-int launch_bwd_prologue(void* zero, size_t zero_bytes, const uint2* ranges, const uint32_t* tile_last, int tiles,
-                        uint32_t* order, cudaStream_t stream);
+int launch_bwd_prologue(void* zero, size_t zero_bytes, const int* radii, int P, const uint2* ranges,
+                        const uint32_t* tile_last, int tiles, uint32_t* order, cudaStream_t stream);
 int launch_blend_fwd(const BlendFwdParams& p, int nw, cudaStream_t stream);
 int launch_blend_bwd(const BlendBwdParams& p, int nw, cudaStream_t stream);
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream);
