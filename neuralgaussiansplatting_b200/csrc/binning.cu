@@ -293,6 +293,9 @@ sort_scan_hist_kernel(uint32_t* hist) {
 #ifndef B200S_SORT_MINB
 #define B200S_SORT_MINB 3
 #endif
+#ifndef B200S_RANK_COUNT_DEFAULT
+#define B200S_RANK_COUNT_DEFAULT 0
+#endif
 constexpr int SORT_MINB = B200S_SORT_MINB;   // resident CTAs per SM requested from ptxas (register cap)
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr int SORT_CNT_STRIDE = SORT_RADIX + 1;      // + sentinel digit for padding items
@@ -426,6 +429,194 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         B200S_CHECK(dst < n);
         keys_out[dst] = kk;
         vals_out[dst] = s_vals[i];
+    }
+}
+
+// ---------------------------------------------------------------- sort, counting rank
+// The same stable 8-bit pass ranked WITHOUT match.any / vote. One MATCH costs ~70 SM cycles on the ADU
+// pipe and a tile needs 128 of them, which bounds the pass above (ncu: ADU 62 %, issue slots 25 % busy).
+// Here the tile is stably partitioned in shared memory by the two nibbles of the digit. Each round:
+// every thread owns 16 CONSECUTIVE keys (blocked order), counts their nibbles in a private row of byte
+// counters (remembering, per key, how many equal nibbles it had seen: the key's rank inside the thread),
+// the counts are scanned in (nibble-major, thread-minor) order — shuffles inside a warp on 16-bit packed
+// fields, 16 threads for the 8 x 16 warp totals — and the keys move to their ranks. After the second
+// round the tile is in digit order; digit boundaries come from a binary search, and the chained
+// look-back + global scatter are those of the kernel above. Only LDS / STS / SHFL / integer ALU.
+constexpr int CR_STRIDE = SORT_ITEMS + 1;   // padded row of a thread's 16 keys: conflict-free blocked access
+constexpr int CR_ROW = 9;                   // words of a thread's private counter / base row (odd: conflict-free)
+constexpr size_t SORT_CR_SMEM = (size_t)SORT_THREADS * CR_STRIDE * 4 * 2 + (size_t)SORT_THREADS * CR_ROW * 4 +
+                                (size_t)SORT_WARPS * 8 * 4 * 2 + (size_t)(SORT_RADIX + 1) * 4 * 2 + 64;
+static_assert(SORT_ITEMS == 16 && SORT_THREADS == 256 && SORT_RADIX_BITS == 8, "counting-rank geometry");
+
+__device__ __forceinline__ uint32_t cr_phys(uint32_t i) { return i + (i >> 4); }
+
+__global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
+sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                           uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                           B200sHeader* header, const uint32_t* __restrict__ n_ptr, int64_t capacity, int shift,
+                           const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* s_keys = reinterpret_cast<uint32_t*>(smem_raw);          // [256][17], logical position i at cr_phys(i)
+    uint32_t* s_vals = s_keys + SORT_THREADS * CR_STRIDE;
+    uint32_t* s_row = s_vals + SORT_THREADS * CR_STRIDE;               // [256][9] private rows
+    uint32_t* s_wtot = s_row + SORT_THREADS * CR_ROW;                  // [warps][8] warp totals, 2 nibble values per word
+    uint32_t* s_comb = s_wtot + SORT_WARPS * 8;                        // [warps][8] nibble start + warp prefix, packed
+    uint32_t* s_dstart = s_comb + SORT_WARPS * 8;                      // [257] tile-local digit start
+    uint32_t* s_gbase = s_dstart + (SORT_RADIX + 1);                   // [257] global dst - local pos
+    uint32_t* s_misc = s_gbase + (SORT_RADIX + 1);                     // [0] tile id
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t n = *n_ptr;
+    if ((int64_t)n > capacity) n = 0;
+    const uint32_t num_tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    if (tid == 0) s_misc[0] = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_misc[0];
+    if (tile >= num_tiles) return;
+    const uint32_t tile_base = tile * SORT_TILE;
+    const uint32_t tile_n = min((uint32_t)SORT_TILE, n - tile_base);
+
+    // blocked load: thread t owns tile positions [16t, 16t + 16). Padding items (key ~0: digit 255 in every
+    // pass, behind every real item by stability) are never written out.
+    uint32_t key[SORT_ITEMS], val[SORT_ITEMS];
+    {
+        const uint32_t i0 = tile_base + (uint32_t)tid * SORT_ITEMS;
+#pragma unroll
+        for (int q = 0; q < SORT_ITEMS / 4; ++q) {
+            const uint32_t i = i0 + 4 * q;
+            if (i + 4 <= n) {
+                const uint4 kk = __ldg(reinterpret_cast<const uint4*>(keys_in + i));
+                const uint4 vv = __ldg(reinterpret_cast<const uint4*>(vals_in + i));
+                key[4 * q] = kk.x; key[4 * q + 1] = kk.y; key[4 * q + 2] = kk.z; key[4 * q + 3] = kk.w;
+                val[4 * q] = vv.x; val[4 * q + 1] = vv.y; val[4 * q + 2] = vv.z; val[4 * q + 3] = vv.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const bool ok = i + j < n;
+                    key[4 * q + j] = ok ? keys_in[i + j] : ~0u;
+                    val[4 * q + j] = ok ? vals_in[i + j] : 0u;
+                }
+            }
+        }
+    }
+
+    uint32_t* row = s_row + tid * CR_ROW;
+    unsigned char* row8 = reinterpret_cast<unsigned char*>(row);
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const int sh = shift + 4 * r;
+        if (r == 1) {
+#pragma unroll
+            for (int k = 0; k < SORT_ITEMS; ++k) {
+                key[k] = s_keys[tid * CR_STRIDE + k];
+                val[k] = s_vals[tid * CR_STRIDE + k];
+            }
+        }
+        row[0] = 0u; row[1] = 0u; row[2] = 0u; row[3] = 0u;
+        uint32_t prev_lo = 0, prev_hi = 0;     // 4-bit fields: equal nibbles among this thread's earlier keys
+#pragma unroll
+        for (int k = 0; k < SORT_ITEMS; ++k) {
+            const uint32_t v = (key[k] >> sh) & 15u;
+            const uint32_t c = row8[v];
+            row8[v] = (unsigned char)(c + 1u);
+            if (k < 8) prev_lo |= c << (4 * k); else prev_hi |= c << (4 * (k - 8));
+        }
+        // own counts as 16-bit fields: word m holds nibble values 2m (low half) and 2m + 1 (high half)
+        uint32_t W[8], own[8];
+        {
+            const uint32_t c0 = row[0], c1 = row[1], c2 = row[2], c3 = row[3];
+            W[0] = __byte_perm(c0, 0u, 0x4140); W[1] = __byte_perm(c0, 0u, 0x4342);
+            W[2] = __byte_perm(c1, 0u, 0x4140); W[3] = __byte_perm(c1, 0u, 0x4342);
+            W[4] = __byte_perm(c2, 0u, 0x4140); W[5] = __byte_perm(c2, 0u, 0x4342);
+            W[6] = __byte_perm(c3, 0u, 0x4140); W[7] = __byte_perm(c3, 0u, 0x4342);
+        }
+#pragma unroll
+        for (int m = 0; m < 8; ++m) own[m] = W[m];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+            for (int m = 0; m < 8; ++m) {
+                const uint32_t t = __shfl_up_sync(FULL_MASK, W[m], o);
+                if (lane >= o) W[m] += t;          // fields stay <= 512: no carry between them
+            }
+        }
+        if (lane == 31) {
+#pragma unroll
+            for (int m = 0; m < 8; ++m) s_wtot[warp * 8 + m] = W[m];
+        }
+        __syncthreads();
+        if (tid < 16) {
+            // thread v: prefix over warps of nibble value v, then the exclusive scan over the 16 values
+            const uint32_t v = (uint32_t)tid;
+            uint32_t run = 0, pre[SORT_WARPS];
+#pragma unroll
+            for (int w = 0; w < SORT_WARPS; ++w) {
+                const uint32_t word = s_wtot[w * 8 + (v >> 1)];
+                pre[w] = run;
+                run += (word >> ((v & 1u) * 16u)) & 0xffffu;
+            }
+            uint32_t incl = run;
+#pragma unroll
+            for (int o = 1; o < 16; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const uint32_t start = incl - run;
+            unsigned short* comb16 = reinterpret_cast<unsigned short*>(s_comb);
+#pragma unroll
+            for (int w = 0; w < SORT_WARPS; ++w) comb16[w * 16 + v] = (unsigned short)(start + pre[w]);   // <= 4096
+        }
+        __syncthreads();
+        // base of (nibble value, this thread) = start + earlier warps + earlier lanes; packed, fields <= 4096
+#pragma unroll
+        for (int m = 0; m < 8; ++m) row[m] = s_comb[warp * 8 + m] + W[m] - own[m];
+#pragma unroll
+        for (int k = 0; k < SORT_ITEMS; ++k) {
+            const uint32_t v = (key[k] >> sh) & 15u;
+            const uint32_t word = row[v >> 1];
+            const uint32_t base = (word >> ((v & 1u) * 16u)) & 0xffffu;
+            const uint32_t c = ((k < 8 ? prev_lo : prev_hi) >> (4 * (k & 7))) & 15u;
+            const uint32_t pos = base + c;
+            B200S_CHECK(pos < (uint32_t)SORT_TILE);
+            const uint32_t ph = cr_phys(pos);
+            s_keys[ph] = key[k];
+            s_vals[ph] = val[k];
+        }
+        __syncthreads();
+    }
+
+    // digit boundaries of the sorted tile: thread d finds the first position whose digit is >= d
+    {
+        const uint32_t d = (uint32_t)tid;
+        uint32_t lo = 0, hi = tile_n;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            const uint32_t kd = (s_keys[cr_phys(mid)] >> shift) & (SORT_RADIX - 1);
+            if (kd < d) lo = mid + 1; else hi = mid;
+        }
+        s_dstart[d] = lo;
+        if (tid == 0) s_dstart[SORT_RADIX] = tile_n;
+    }
+    __syncthreads();
+    const uint32_t dstart = s_dstart[tid];
+    const uint32_t count = s_dstart[tid + 1] - dstart;
+    uint32_t* lb = lookback + (size_t)tile * SORT_RADIX + tid;
+    st_volatile_u32(lb, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
+    uint32_t excl = 0;
+    if (tile != 0) {
+        excl = thread_lookback(lookback + tid, SORT_RADIX, (int64_t)tile, header);
+        st_volatile_u32(lb, ((excl + count) << 2) | FLAG_INCL);
+    }
+    s_gbase[tid] = bin_base[tid] + excl - dstart;
+    __syncthreads();
+    for (uint32_t i = tid; i < tile_n; i += SORT_THREADS) {
+        const uint32_t ph = cr_phys(i);
+        const uint32_t kk = s_keys[ph];
+        const uint32_t d = (kk >> shift) & (SORT_RADIX - 1);
+        const uint32_t dst = s_gbase[d] + i;
+        B200S_CHECK(dst < n);
+        keys_out[dst] = kk;
+        vals_out[dst] = s_vals[ph];
     }
 }
 
@@ -745,10 +936,22 @@ static bool rank_by_match(int which, int pass) {
     static int mask = [] { const char* v = getenv("B200S_RANK_MATCH"); return v && *v ? (int)strtol(v, nullptr, 0) : 0xff; }();
     return (mask >> (which * 4 + pass)) & 1;
 }
+// B200S_RANK_COUNT = bit mask over (which * 4 + pass): passes ranked by the counting kernel (no MATCH / VOTE).
+static bool rank_by_count(int which, int pass) {
+    static int mask = [] { const char* v = getenv("B200S_RANK_COUNT"); return v && *v ? (int)strtol(v, nullptr, 0) : B200S_RANK_COUNT_DEFAULT; }();
+    return (mask >> (which * 4 + pass)) & 1;
+}
 static int set_sort_attr() {
     B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
     B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+    B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_CR_SMEM);
     return 0;
+}
+using SortPassFn = void (*)(const uint32_t*, const uint32_t*, uint32_t*, uint32_t*, B200sHeader*, const uint32_t*, int64_t,
+                            int, const uint32_t*, uint32_t*, uint32_t*);
+static void sort_pass_kernel(int which, int pass, SortPassFn* fn, size_t* smem) {
+    if (rank_by_count(which, pass)) { *fn = sort_onesweep_count_kernel; *smem = SORT_CR_SMEM; }
+    else { *fn = rank_by_match(which, pass) ? sort_onesweep_kernel<true> : sort_onesweep_kernel<false>; *smem = SORT_SMEM; }
 }
 
 // Stage 1b: point_offsets + num_rendered, compaction of the visible Gaussians, depth sort.
@@ -778,8 +981,9 @@ int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t 
         int cur = 0;
         for (int p = 0; p < DEPTH_PASSES; ++p) {
             count_launch();
-            auto kern = rank_by_match(0, p) ? sort_onesweep_kernel<true> : sort_onesweep_kernel<false>;
-            kern<<<(unsigned)g.depth_tiles, SORT_THREADS, SORT_SMEM, stream>>>(
+            SortPassFn kern; size_t smem;
+            sort_pass_kernel(0, p, &kern, &smem);
+            kern<<<(unsigned)g.depth_tiles, SORT_THREADS, smem, stream>>>(
                 g.vis_keys[cur], g.vis_ids[cur], g.vis_keys[cur ^ 1], g.vis_ids[cur ^ 1], g.header, n_ptr,
                 (int64_t)P, p * SORT_RADIX_BITS, g.depth_hist + p * SORT_RADIX,
                 g.depth_lookback + (size_t)p * g.depth_tiles * SORT_RADIX, g.counters + CTR_DEPTH_TICKET0 + p);
@@ -845,8 +1049,9 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
         B200S_AFTER_LAUNCH(stream, debug);
         for (int p = 0; p < passes; ++p) {
             count_launch();
-            auto kern = rank_by_match(1, p) ? sort_onesweep_kernel<true> : sort_onesweep_kernel<false>;
-            kern<<<(unsigned)sort_tiles, SORT_THREADS, SORT_SMEM, stream>>>(
+            SortPassFn kern; size_t smem;
+            sort_pass_kernel(1, p, &kern, &smem);
+            kern<<<(unsigned)sort_tiles, SORT_THREADS, smem, stream>>>(
                 bw.keys[cur], bw.vals[cur], bw.keys[cur ^ 1], bw.vals[cur ^ 1], g.header, &g.header->num_rendered,
                 capacity, p * SORT_RADIX_BITS, bw.hist + p * SORT_RADIX,
                 bw.lookback + (size_t)p * bw.sort_tiles * SORT_RADIX, g.counters + CTR_SORT_TICKET0 + p);
