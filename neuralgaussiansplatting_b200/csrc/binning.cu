@@ -270,23 +270,38 @@ sort_histogram_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restr
     }
 }
 
-// One block per pass: in-place exclusive scan of the 256 digit counts.
+// One block per pass: in-place exclusive scan of the 256 digit counts. With from_diff the input is a
+// DIFFERENCE array (+c where a range of digits starts, -c behind its end; see sorted_scan_kernel): it is
+// integrated into counts first (modulo 2^32, so the negative entries are exact).
 __global__ void __launch_bounds__(SORT_RADIX)
-sort_scan_hist_kernel(uint32_t* hist) {
-    __shared__ uint32_t s_warp[SORT_RADIX / 32];
+sort_scan_hist_kernel(uint32_t* hist, int from_diff) {
+    __shared__ uint32_t s_warp[2][SORT_RADIX / 32];
     uint32_t* h = hist + blockIdx.x * SORT_RADIX;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t c = h[tid];
+    uint32_t c = h[tid];
+    if (from_diff) {
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(FULL_MASK, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_warp[1][warp] = incl;
+        __syncthreads();
+        uint32_t wex = 0;
+        for (int w = 0; w < warp; ++w) wex += s_warp[1][w];
+        c = wex + incl;
+    }
     uint32_t incl = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t t = __shfl_up_sync(FULL_MASK, incl, o);
         if (lane >= o) incl += t;
     }
-    if (lane == 31) s_warp[warp] = incl;
+    if (lane == 31) s_warp[0][warp] = incl;
     __syncthreads();
     uint32_t wex = 0;
-    for (int w = 0; w < warp; ++w) wex += s_warp[w];
+    for (int w = 0; w < warp; ++w) wex += s_warp[0][w];
     h[tid] = wex + incl - c;
 }
 
@@ -295,6 +310,12 @@ sort_scan_hist_kernel(uint32_t* hist) {
 #endif
 #ifndef B200S_RANK_COUNT_DEFAULT
 #define B200S_RANK_COUNT_DEFAULT 0
+#endif
+#ifndef B200S_XY_KEYS_DEFAULT
+#define B200S_XY_KEYS_DEFAULT 0
+#endif
+#ifndef B200S_FUSE_EXPAND_DEFAULT
+#define B200S_FUSE_EXPAND_DEFAULT 0
 #endif
 constexpr int SORT_MINB = B200S_SORT_MINB;   // resident CTAs per SM requested from ptxas (register cap)
 constexpr int SORT_WARPS = SORT_THREADS / 32;
@@ -444,63 +465,44 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
 // look-back + global scatter are those of the kernel above. Only LDS / STS / SHFL / integer ALU.
 constexpr int CR_STRIDE = SORT_ITEMS + 1;   // padded row of a thread's 16 keys: conflict-free blocked access
 constexpr int CR_ROW = 9;                   // words of a thread's private counter / base row (odd: conflict-free)
-constexpr size_t SORT_CR_SMEM = (size_t)SORT_THREADS * CR_STRIDE * 4 * 2 + (size_t)SORT_THREADS * CR_ROW * 4 +
-                                (size_t)SORT_WARPS * 8 * 4 * 2 + (size_t)(SORT_RADIX + 1) * 4 * 2 + 64;
+constexpr size_t CR_ARRAY_BYTES = (size_t)SORT_THREADS * CR_STRIDE * 4 * 2 + (size_t)SORT_THREADS * CR_ROW * 4;
+constexpr size_t CR_TAIL_BYTES = (size_t)SORT_WARPS * 8 * 4 * 2 + (size_t)(SORT_RADIX + 1) * 4 * 2 + 64;
+constexpr size_t SORT_CR_SMEM = CR_ARRAY_BYTES + CR_TAIL_BYTES;
 static_assert(SORT_ITEMS == 16 && SORT_THREADS == 256 && SORT_RADIX_BITS == 8, "counting-rank geometry");
+static_assert(CR_ARRAY_BYTES % 16 == 0, "tail alignment");
+
+struct CrSmem {
+    uint32_t* keys;     // [256][17], logical position i at cr_phys(i)
+    uint32_t* vals;
+    uint32_t* row;      // [256][9] private rows
+    uint32_t* wtot;     // [warps][8] warp totals, 2 nibble values per word
+    uint32_t* comb;     // [warps][8] nibble start + warp prefix, packed
+    uint32_t* dstart;   // [257] tile-local digit start
+    uint32_t* gbase;    // [257] global dst - local pos
+    uint32_t* misc;     // [0] tile id
+};
+__device__ __forceinline__ CrSmem cr_carve(unsigned char* arrays, unsigned char* tail) {
+    CrSmem sm;
+    sm.keys = reinterpret_cast<uint32_t*>(arrays);
+    sm.vals = sm.keys + SORT_THREADS * CR_STRIDE;
+    sm.row = sm.vals + SORT_THREADS * CR_STRIDE;
+    sm.wtot = reinterpret_cast<uint32_t*>(tail);
+    sm.comb = sm.wtot + SORT_WARPS * 8;
+    sm.dstart = sm.comb + SORT_WARPS * 8;
+    sm.gbase = sm.dstart + (SORT_RADIX + 1);
+    sm.misc = sm.gbase + (SORT_RADIX + 1);
+    return sm;
+}
 
 __device__ __forceinline__ uint32_t cr_phys(uint32_t i) { return i + (i >> 4); }
 
-__global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
-sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                           uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-                           B200sHeader* header, const uint32_t* __restrict__ n_ptr, int64_t capacity, int shift,
-                           const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint32_t* s_keys = reinterpret_cast<uint32_t*>(smem_raw);          // [256][17], logical position i at cr_phys(i)
-    uint32_t* s_vals = s_keys + SORT_THREADS * CR_STRIDE;
-    uint32_t* s_row = s_vals + SORT_THREADS * CR_STRIDE;               // [256][9] private rows
-    uint32_t* s_wtot = s_row + SORT_THREADS * CR_ROW;                  // [warps][8] warp totals, 2 nibble values per word
-    uint32_t* s_comb = s_wtot + SORT_WARPS * 8;                        // [warps][8] nibble start + warp prefix, packed
-    uint32_t* s_dstart = s_comb + SORT_WARPS * 8;                      // [257] tile-local digit start
-    uint32_t* s_gbase = s_dstart + (SORT_RADIX + 1);                   // [257] global dst - local pos
-    uint32_t* s_misc = s_gbase + (SORT_RADIX + 1);                     // [0] tile id
-
+// Stable partition of the tile's 4,096 (key, value) pairs by the 8-bit digit at `shift`. Input: blocked order in
+// registers (thread t holds tile positions [16t, 16t + 16)); result at cr_phys() positions of sm.keys / sm.vals.
+// Ends with a __syncthreads().
+__device__ __forceinline__ void cr_sort_tile(uint32_t (&key)[SORT_ITEMS], uint32_t (&val)[SORT_ITEMS], const CrSmem& sm,
+                                             int shift) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    uint32_t n = *n_ptr;
-    if ((int64_t)n > capacity) n = 0;
-    const uint32_t num_tiles = (n + SORT_TILE - 1) / SORT_TILE;
-    if (tid == 0) s_misc[0] = atomicAdd(ticket, 1u);
-    __syncthreads();
-    const uint32_t tile = s_misc[0];
-    if (tile >= num_tiles) return;
-    const uint32_t tile_base = tile * SORT_TILE;
-    const uint32_t tile_n = min((uint32_t)SORT_TILE, n - tile_base);
-
-    // blocked load: thread t owns tile positions [16t, 16t + 16). Padding items (key ~0: digit 255 in every
-    // pass, behind every real item by stability) are never written out.
-    uint32_t key[SORT_ITEMS], val[SORT_ITEMS];
-    {
-        const uint32_t i0 = tile_base + (uint32_t)tid * SORT_ITEMS;
-#pragma unroll
-        for (int q = 0; q < SORT_ITEMS / 4; ++q) {
-            const uint32_t i = i0 + 4 * q;
-            if (i + 4 <= n) {
-                const uint4 kk = __ldg(reinterpret_cast<const uint4*>(keys_in + i));
-                const uint4 vv = __ldg(reinterpret_cast<const uint4*>(vals_in + i));
-                key[4 * q] = kk.x; key[4 * q + 1] = kk.y; key[4 * q + 2] = kk.z; key[4 * q + 3] = kk.w;
-                val[4 * q] = vv.x; val[4 * q + 1] = vv.y; val[4 * q + 2] = vv.z; val[4 * q + 3] = vv.w;
-            } else {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const bool ok = i + j < n;
-                    key[4 * q + j] = ok ? keys_in[i + j] : ~0u;
-                    val[4 * q + j] = ok ? vals_in[i + j] : 0u;
-                }
-            }
-        }
-    }
-
-    uint32_t* row = s_row + tid * CR_ROW;
+    uint32_t* row = sm.row + tid * CR_ROW;
     unsigned char* row8 = reinterpret_cast<unsigned char*>(row);
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
@@ -508,8 +510,8 @@ sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t*
         if (r == 1) {
 #pragma unroll
             for (int k = 0; k < SORT_ITEMS; ++k) {
-                key[k] = s_keys[tid * CR_STRIDE + k];
-                val[k] = s_vals[tid * CR_STRIDE + k];
+                key[k] = sm.keys[tid * CR_STRIDE + k];
+                val[k] = sm.vals[tid * CR_STRIDE + k];
             }
         }
         row[0] = 0u; row[1] = 0u; row[2] = 0u; row[3] = 0u;
@@ -542,7 +544,7 @@ sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t*
         }
         if (lane == 31) {
 #pragma unroll
-            for (int m = 0; m < 8; ++m) s_wtot[warp * 8 + m] = W[m];
+            for (int m = 0; m < 8; ++m) sm.wtot[warp * 8 + m] = W[m];
         }
         __syncthreads();
         if (tid < 16) {
@@ -551,7 +553,7 @@ sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t*
             uint32_t run = 0, pre[SORT_WARPS];
 #pragma unroll
             for (int w = 0; w < SORT_WARPS; ++w) {
-                const uint32_t word = s_wtot[w * 8 + (v >> 1)];
+                const uint32_t word = sm.wtot[w * 8 + (v >> 1)];
                 pre[w] = run;
                 run += (word >> ((v & 1u) * 16u)) & 0xffffu;
             }
@@ -562,14 +564,14 @@ sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t*
                 if (lane >= o) incl += t;
             }
             const uint32_t start = incl - run;
-            unsigned short* comb16 = reinterpret_cast<unsigned short*>(s_comb);
+            unsigned short* comb16 = reinterpret_cast<unsigned short*>(sm.comb);
 #pragma unroll
             for (int w = 0; w < SORT_WARPS; ++w) comb16[w * 16 + v] = (unsigned short)(start + pre[w]);   // <= 4096
         }
         __syncthreads();
         // base of (nibble value, this thread) = start + earlier warps + earlier lanes; packed, fields <= 4096
 #pragma unroll
-        for (int m = 0; m < 8; ++m) row[m] = s_comb[warp * 8 + m] + W[m] - own[m];
+        for (int m = 0; m < 8; ++m) row[m] = sm.comb[warp * 8 + m] + W[m] - own[m];
 #pragma unroll
         for (int k = 0; k < SORT_ITEMS; ++k) {
             const uint32_t v = (key[k] >> sh) & 15u;
@@ -579,27 +581,34 @@ sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t*
             const uint32_t pos = base + c;
             B200S_CHECK(pos < (uint32_t)SORT_TILE);
             const uint32_t ph = cr_phys(pos);
-            s_keys[ph] = key[k];
-            s_vals[ph] = val[k];
+            sm.keys[ph] = key[k];
+            sm.vals[ph] = val[k];
         }
         __syncthreads();
     }
+}
 
-    // digit boundaries of the sorted tile: thread d finds the first position whose digit is >= d
+// The sorted tile leaves for global memory: digit boundaries by binary search (thread d finds the first
+// position whose digit is >= d), chained look-back per digit, coalesced scatter.
+__device__ __forceinline__ void cr_scatter_tile(const CrSmem& sm, uint32_t tile, uint32_t tile_n, uint32_t n, int shift,
+                                                const uint32_t* __restrict__ bin_base, uint32_t* lookback,
+                                                B200sHeader* header, uint32_t* __restrict__ keys_out,
+                                                uint32_t* __restrict__ vals_out) {
+    const int tid = threadIdx.x;
     {
         const uint32_t d = (uint32_t)tid;
         uint32_t lo = 0, hi = tile_n;
         while (lo < hi) {
             const uint32_t mid = (lo + hi) >> 1;
-            const uint32_t kd = (s_keys[cr_phys(mid)] >> shift) & (SORT_RADIX - 1);
+            const uint32_t kd = (sm.keys[cr_phys(mid)] >> shift) & (SORT_RADIX - 1);
             if (kd < d) lo = mid + 1; else hi = mid;
         }
-        s_dstart[d] = lo;
-        if (tid == 0) s_dstart[SORT_RADIX] = tile_n;
+        sm.dstart[d] = lo;
+        if (tid == 0) sm.dstart[SORT_RADIX] = tile_n;
     }
     __syncthreads();
-    const uint32_t dstart = s_dstart[tid];
-    const uint32_t count = s_dstart[tid + 1] - dstart;
+    const uint32_t dstart = sm.dstart[tid];
+    const uint32_t count = sm.dstart[tid + 1] - dstart;
     uint32_t* lb = lookback + (size_t)tile * SORT_RADIX + tid;
     st_volatile_u32(lb, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
     uint32_t excl = 0;
@@ -607,17 +616,62 @@ sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t*
         excl = thread_lookback(lookback + tid, SORT_RADIX, (int64_t)tile, header);
         st_volatile_u32(lb, ((excl + count) << 2) | FLAG_INCL);
     }
-    s_gbase[tid] = bin_base[tid] + excl - dstart;
+    sm.gbase[tid] = bin_base[tid] + excl - dstart;
     __syncthreads();
     for (uint32_t i = tid; i < tile_n; i += SORT_THREADS) {
         const uint32_t ph = cr_phys(i);
-        const uint32_t kk = s_keys[ph];
+        const uint32_t kk = sm.keys[ph];
         const uint32_t d = (kk >> shift) & (SORT_RADIX - 1);
-        const uint32_t dst = s_gbase[d] + i;
+        const uint32_t dst = sm.gbase[d] + i;
         B200S_CHECK(dst < n);
         keys_out[dst] = kk;
-        vals_out[dst] = s_vals[ph];
+        vals_out[dst] = sm.vals[ph];
     }
+}
+
+__global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
+sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                           uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                           B200sHeader* header, const uint32_t* __restrict__ n_ptr, int64_t capacity, int shift,
+                           const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const CrSmem sm = cr_carve(smem_raw, smem_raw + CR_ARRAY_BYTES);
+    const int tid = threadIdx.x;
+    uint32_t n = *n_ptr;
+    if ((int64_t)n > capacity) n = 0;
+    const uint32_t num_tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    if (tid == 0) sm.misc[0] = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = sm.misc[0];
+    if (tile >= num_tiles) return;
+    const uint32_t tile_base = tile * SORT_TILE;
+    const uint32_t tile_n = min((uint32_t)SORT_TILE, n - tile_base);
+
+    // blocked load: thread t owns tile positions [16t, 16t + 16). Padding items (key ~0: digit 255 in every
+    // pass, behind every real item by stability) are never written out.
+    uint32_t key[SORT_ITEMS], val[SORT_ITEMS];
+    {
+        const uint32_t i0 = tile_base + (uint32_t)tid * SORT_ITEMS;
+#pragma unroll
+        for (int q = 0; q < SORT_ITEMS / 4; ++q) {
+            const uint32_t i = i0 + 4 * q;
+            if (i + 4 <= n) {
+                const uint4 kk = __ldg(reinterpret_cast<const uint4*>(keys_in + i));
+                const uint4 vv = __ldg(reinterpret_cast<const uint4*>(vals_in + i));
+                key[4 * q] = kk.x; key[4 * q + 1] = kk.y; key[4 * q + 2] = kk.z; key[4 * q + 3] = kk.w;
+                val[4 * q] = vv.x; val[4 * q + 1] = vv.y; val[4 * q + 2] = vv.z; val[4 * q + 3] = vv.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const bool ok = i + j < n;
+                    key[4 * q + j] = ok ? keys_in[i + j] : ~0u;
+                    val[4 * q + j] = ok ? vals_in[i + j] : 0u;
+                }
+            }
+        }
+    }
+    cr_sort_tile(key, val, sm, shift);
+    cr_scatter_tile(sm, tile, tile_n, n, shift, bin_base, lookback, header, keys_out, vals_out);
 }
 
 // ----------------------------------------------------------------------------- expand
@@ -639,9 +693,10 @@ __global__ void __launch_bounds__(SS_THREADS)
 sorted_scan_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __restrict__ rec,
                    uint32_t* __restrict__ run_end, uint32_t* __restrict__ run_rmin, uint32_t* __restrict__ run_rwh,
                    uint32_t* __restrict__ block_first, B200sHeader* header, int64_t capacity,
-                   uint32_t* status, uint32_t* ticket) {
+                   uint32_t* status, uint32_t* ticket, uint32_t* __restrict__ hist, int xy_keys) {
     __shared__ uint32_t s_warp[SS_THREADS / 32];
     __shared__ uint32_t s_block, s_prefix;
+    __shared__ uint32_t s_diff[2 * SORT_RADIX];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_vis = header->num_visible;
     if ((int64_t)header->num_rendered > capacity) {
@@ -649,6 +704,7 @@ sorted_scan_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __re
         return;
     }
     if (tid == 0) s_block = atomicAdd(ticket, 1u);
+    if (xy_keys) for (int i = tid; i < 2 * SORT_RADIX; i += SS_THREADS) s_diff[i] = 0u;
     __syncthreads();
     const uint32_t block = s_block;
     const uint32_t g0 = block * EXP_TILE + tid * EXP_ITEMS;
@@ -663,6 +719,18 @@ sorted_scan_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __re
             const float4 q2 = rec[sorted_ids[g0 + k]].q2;
             rmin[k] = __float_as_uint(q2.z); rwh[k] = __float_as_uint(q2.w);
             cnt[k] = (rwh[k] & 0xffffu) * (rwh[k] >> 16);
+            if (xy_keys && cnt[k] != 0u) {
+                // digit histograms of the (x, y) tile keys as range-adds: the w x h rectangle puts h instances on
+                // every column digit x in [xmin, xmin + w) and w on every row digit y in [ymin, ymin + h):
+                // 4 shared-memory atomics per Gaussian instead of 2 per instance in the expansion
+                const uint32_t w = rwh[k] & 0xffffu, h = rwh[k] >> 16;
+                const uint32_t x0 = rmin[k] & 0xffffu, y0 = rmin[k] >> 16;
+                B200S_CHECK(x0 + w <= (uint32_t)SORT_RADIX && y0 + h <= (uint32_t)SORT_RADIX);
+                atomicAdd(&s_diff[x0], h);
+                if (x0 + w < (uint32_t)SORT_RADIX) atomicAdd(&s_diff[x0 + w], 0u - h);
+                atomicAdd(&s_diff[SORT_RADIX + y0], w);
+                if (y0 + h < (uint32_t)SORT_RADIX) atomicAdd(&s_diff[SORT_RADIX + y0 + h], 0u - w);
+            }
         }
         tsum += cnt[k];
     }
@@ -704,13 +772,21 @@ sorted_scan_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __re
             run = end;
         }
     }
+    if (xy_keys) {
+        // every thread's shared-memory atomics precede the __syncthreads() of the scan above
+        for (int i = tid; i < 2 * SORT_RADIX; i += SS_THREADS) {
+            const uint32_t c = s_diff[i];
+            if (c) atomicAdd(&hist[i], c);
+        }
+    }
 }
 
 __global__ void __launch_bounds__(EXP_THREADS)
 expand_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* __restrict__ run_end,
               const uint32_t* __restrict__ run_rmin, const uint32_t* __restrict__ run_rwh,
               const uint32_t* __restrict__ block_first, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
-              int grid_x, int passes, const B200sHeader* header, int64_t capacity, uint32_t* __restrict__ hist) {
+              int grid_x, int passes, const B200sHeader* header, int64_t capacity, uint32_t* __restrict__ hist,
+              int xy_keys) {
     __shared__ uint32_t s_end[OUT_TILE + 1], s_id[OUT_TILE + 1], s_rmin[OUT_TILE + 1], s_rwh[OUT_TILE + 1];
     __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_RADIX];
     const int tid = threadIdx.x;
@@ -763,10 +839,13 @@ expand_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* __restric
                 const uint32_t tile = ((rmin >> 16) + ty) * (uint32_t)grid_x + (rmin & 0xffffu) + tx;
                 B200S_CHECK(w != 0 && ty < (rwh >> 16) && (int64_t)(o + i) < capacity &&
                             tile < (passes >= 4 ? 0xffffffffu : (1u << (passes * SORT_RADIX_BITS))));
-                tk[i] = tile; tv[i] = id;
+                // xy_keys: key = row << 8 | column (same order as the tile id for grids up to 256 x 256); its digit
+                // histograms were accumulated per Gaussian by sorted_scan_kernel
+                tk[i] = xy_keys ? ((((rmin >> 16) + ty) << SORT_RADIX_BITS) | ((rmin & 0xffffu) + tx)) : tile;
+                tv[i] = id;
                 if (++tx == w) { tx = 0; ++ty; }
-                atomicAdd(&s_hist[tile & (SORT_RADIX - 1)], 1u);
-                if (passes > 1) {
+                if (!xy_keys) atomicAdd(&s_hist[tile & (SORT_RADIX - 1)], 1u);
+                if (!xy_keys && passes > 1) {
                     const uint32_t hi_d = tile >> SORT_RADIX_BITS;     // all higher digits at once
                     if (hi_d != hd) {
                         if (hc) {
@@ -779,7 +858,7 @@ expand_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* __restric
                 }
             }
         }
-        if (hc) {
+        if (!xy_keys && hc) {
             for (int p = 1; p < passes; ++p)
                 atomicAdd(&s_hist[p * SORT_RADIX + ((hd >> ((p - 1) * SORT_RADIX_BITS)) & (SORT_RADIX - 1))], hc);
         }
@@ -797,6 +876,7 @@ expand_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* __restric
                 if (o + i < o1) { keys[o + i] = tk[i]; vals[o + i] = tv[i]; }
         }
     }
+    if (xy_keys) return;
     __syncthreads();
     for (int i = tid; i < passes * SORT_RADIX; i += EXP_THREADS) {
         const uint32_t c = s_hist[i];
@@ -804,20 +884,107 @@ expand_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* __restric
     }
 }
 
+// Expansion fused into the first tile pass ((x, y) keys + counting rank): the block GENERATES its 4,096 instances in
+// blocked order (thread t: slots [16t, 16t + 16), one binary search then a walk, as expand_kernel does) and ranks
+// them by column right away, so the unsorted instances never travel through HBM (16 B written + 16 B read per
+// instance) and one launch disappears. The column histogram is already known (sorted_scan_kernel's range-adds).
+constexpr int XP_RUNS = SORT_TILE + 1;                              // Gaussians whose runs can intersect one tile
+constexpr size_t XP_RUN_BYTES = ((size_t)XP_RUNS * 4 + 15) / 16 * 16;
+constexpr size_t XP_UNION_BYTES = 3 * XP_RUN_BYTES > CR_ARRAY_BYTES ? 3 * XP_RUN_BYTES : CR_ARRAY_BYTES;
+constexpr size_t SORT_XP_SMEM = XP_RUN_BYTES + XP_UNION_BYTES + CR_TAIL_BYTES;
+static_assert(SORT_TILE % OUT_TILE == 0, "block_first granularity");
+
+__global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
+expand_sort_count_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* __restrict__ run_end,
+                         const uint32_t* __restrict__ run_rmin, const uint32_t* __restrict__ run_rwh,
+                         const uint32_t* __restrict__ block_first, uint32_t* __restrict__ keys_out,
+                         uint32_t* __restrict__ vals_out, B200sHeader* header, int64_t capacity,
+                         const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* s_end = reinterpret_cast<uint32_t*>(smem_raw);
+    unsigned char* uni = smem_raw + XP_RUN_BYTES;                   // run arrays first, the sort's arrays afterwards
+    uint32_t* s_id = reinterpret_cast<uint32_t*>(uni);
+    uint32_t* s_rmin = reinterpret_cast<uint32_t*>(uni + XP_RUN_BYTES);
+    uint32_t* s_rwh = reinterpret_cast<uint32_t*>(uni + 2 * XP_RUN_BYTES);
+    const CrSmem sm = cr_carve(uni, uni + XP_UNION_BYTES);
+    const int tid = threadIdx.x;
+    uint32_t n = header->num_rendered;
+    if ((int64_t)n > capacity) n = 0;
+    const uint32_t num_tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    if (tid == 0) sm.misc[0] = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = sm.misc[0];
+    if (tile >= num_tiles) return;
+    const uint32_t o0 = tile * SORT_TILE;
+    const uint32_t o1 = min(n, o0 + (uint32_t)SORT_TILE);
+    const uint32_t tile_n = o1 - o0;
+
+    const uint32_t j0 = block_first[tile * (SORT_TILE / OUT_TILE)];
+    const uint32_t n_vis = header->num_visible;
+    const uint32_t jmax = min(n_vis - 1, j0 + (uint32_t)SORT_TILE);
+    for (uint32_t j = j0 + tid; j <= jmax; j += SORT_THREADS) {
+        const uint32_t l = j - j0;
+        s_end[l] = run_end[j];
+        s_id[l] = sorted_ids[j];
+        s_rmin[l] = run_rmin[j];
+        s_rwh[l] = run_rwh[j];
+    }
+    __syncthreads();
+    const int cntj = (int)(jmax - j0) + 1;
+    uint32_t key[SORT_ITEMS], val[SORT_ITEMS];
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; ++i) { key[i] = ~0u; val[i] = 0u; }
+    const uint32_t o = o0 + (uint32_t)tid * SORT_ITEMS;
+    if (o < o1) {
+        int lo = 0, hi = cntj - 1;          // smallest l with s_end[l] > o
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (s_end[mid] > o) hi = mid; else lo = mid + 1;
+        }
+        int l = lo;
+        uint32_t end = s_end[l];
+        uint32_t rwh = s_rwh[l], rmin = s_rmin[l], id = s_id[l];
+        uint32_t w = rwh & 0xffffu;
+        const uint32_t k0 = o - (end - w * (rwh >> 16));
+        uint32_t ty = k0 / w, tx = k0 - ty * w;
+#pragma unroll
+        for (int i = 0; i < SORT_ITEMS; ++i) {
+            if (o + i < o1) {
+                if (o + i >= end) {
+                    ++l;
+                    B200S_CHECK(l < cntj);
+                    end = s_end[l]; rwh = s_rwh[l]; rmin = s_rmin[l]; id = s_id[l];
+                    w = rwh & 0xffffu; tx = 0; ty = 0;
+                }
+                B200S_CHECK(w != 0 && ty < (rwh >> 16) && (rmin >> 16) + ty < (uint32_t)SORT_RADIX &&
+                            (rmin & 0xffffu) + tx < (uint32_t)SORT_RADIX);
+                key[i] = (((rmin >> 16) + ty) << SORT_RADIX_BITS) | ((rmin & 0xffffu) + tx);
+                val[i] = id;
+                if (++tx == w) { tx = 0; ++ty; }
+            }
+        }
+    }
+    __syncthreads();                                                // the run arrays are dead: their space is the sort's
+    cr_sort_tile(key, val, sm, 0);
+    cr_scatter_tile(sm, tile, tile_n, n, 0, bin_base, lookback, header, keys_out, vals_out);
+}
+
 // ----------------------------------------------------------------------------- ranges
 // identifyTileRanges (rasterizer_impl.cu:116-138); `ranges` was cleared beforehand.
 __global__ void __launch_bounds__(256)
 tile_ranges_kernel(const uint32_t* __restrict__ keys, const B200sHeader* header, int64_t capacity,
-                   uint2* __restrict__ ranges) {
+                   uint2* __restrict__ ranges, int xy_keys, int grid_x) {
     uint32_t n = header->num_rendered;
     if ((int64_t)n > capacity) n = 0;
     const int64_t stride = (int64_t)gridDim.x * 256;
     for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
-        const uint32_t cur = keys[i];
+        uint32_t cur = keys[i];
+        if (xy_keys) cur = (cur >> SORT_RADIX_BITS) * (uint32_t)grid_x + (cur & (SORT_RADIX - 1));
         if (i == 0) {
             ranges[cur].x = 0;
         } else {
-            const uint32_t prev = keys[i - 1];
+            uint32_t prev = keys[i - 1];
+            if (xy_keys) prev = (prev >> SORT_RADIX_BITS) * (uint32_t)grid_x + (prev & (SORT_RADIX - 1));
             if (cur != prev) {
                 ranges[prev].y = (uint32_t)i;
                 ranges[cur].x = (uint32_t)i;
@@ -945,6 +1112,7 @@ static int set_sort_attr() {
     B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
     B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
     B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_CR_SMEM);
+    B200S_SET_FUNC_ATTR_ONCE(expand_sort_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_XP_SMEM);
     return 0;
 }
 using SortPassFn = void (*)(const uint32_t*, const uint32_t*, uint32_t*, uint32_t*, B200sHeader*, const uint32_t*, int64_t,
@@ -976,7 +1144,7 @@ int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t 
         count_launch(2);
         sort_histogram_kernel<<<hb, 256, 0, stream>>>(g.vis_keys[0], n_ptr, DEPTH_PASSES, g.depth_hist);
         B200S_AFTER_LAUNCH(stream, debug);
-        sort_scan_hist_kernel<<<DEPTH_PASSES, SORT_RADIX, 0, stream>>>(g.depth_hist);
+        sort_scan_hist_kernel<<<DEPTH_PASSES, SORT_RADIX, 0, stream>>>(g.depth_hist, 0);
         B200S_AFTER_LAUNCH(stream, debug);
         int cur = 0;
         for (int p = 0; p < DEPTH_PASSES; ++p) {
@@ -1020,6 +1188,12 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
                    int tiles, uint2* ranges, int* final_buf, bool debug, cudaStream_t stream) {
     { const int rc_attr = set_sort_attr(); if (rc_attr) return rc_attr; }
     const int passes = sort_num_passes(tiles);
+    // (x, y) keys: row << 8 | column instead of the tile id, when that is still a 2-pass sort. Same order, but the
+    // two digits are the tile coordinates themselves, so their histograms are range-adds per Gaussian.
+    static const int xy_env = [] { const char* v = getenv("B200S_XY_KEYS"); return v && *v ? atoi(v) : B200S_XY_KEYS_DEFAULT; }();
+    const int xy_keys = (xy_env && passes == 2 && grid_x <= SORT_RADIX && tiles / grid_x <= SORT_RADIX) ? 1 : 0;
+    static const int fuse_env = [] { const char* v = getenv("B200S_FUSE_EXPAND"); return v && *v ? atoi(v) : B200S_FUSE_EXPAND_DEFAULT; }();
+    const bool fuse_expand = xy_keys && fuse_env && rank_by_count(1, 0);
     if (n_hint > capacity) n_hint = capacity;
     if (n_hint < 1) n_hint = 1;
     {
@@ -1033,22 +1207,32 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
         count_launch(2);
         sorted_scan_kernel<<<(P + EXP_TILE - 1) / EXP_TILE, SS_THREADS, 0, stream>>>(
             g.vis_ids[0], g.rec, g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, g.header, capacity,
-            g.exp_status, g.counters + CTR_EXPAND_TICKET);
+            g.exp_status, g.counters + CTR_EXPAND_TICKET, bw.hist, xy_keys);
         B200S_AFTER_LAUNCH(stream, debug);
-        expand_kernel<<<(unsigned)((n_hint + OUT_TILE - 1) / OUT_TILE), EXP_THREADS, 0, stream>>>(
-            g.vis_ids[0], g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, bw.keys[0], bw.vals[0],
-            grid_x, passes, g.header, capacity, bw.hist);
-        B200S_AFTER_LAUNCH(stream, debug);
+        if (!fuse_expand) {
+            expand_kernel<<<(unsigned)((n_hint + OUT_TILE - 1) / OUT_TILE), EXP_THREADS, 0, stream>>>(
+                g.vis_ids[0], g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, bw.keys[0], bw.vals[0],
+                grid_x, passes, g.header, capacity, bw.hist, xy_keys);
+            B200S_AFTER_LAUNCH(stream, debug);
+        }
     }
     const int64_t sort_tiles = (n_hint + SORT_TILE - 1) / SORT_TILE;
     int cur = 0;
     {
         ProfScope ps(B200S_STAGE_SORT, stream);
         count_launch();
-        sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, stream>>>(bw.hist);
+        sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, stream>>>(bw.hist, xy_keys);
         B200S_AFTER_LAUNCH(stream, debug);
         for (int p = 0; p < passes; ++p) {
             count_launch();
+            if (p == 0 && fuse_expand && P > 0) {
+                expand_sort_count_kernel<<<(unsigned)sort_tiles, SORT_THREADS, SORT_XP_SMEM, stream>>>(
+                    g.vis_ids[0], g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, bw.keys[1], bw.vals[1],
+                    g.header, capacity, bw.hist, bw.lookback, g.counters + CTR_SORT_TICKET0);
+                B200S_AFTER_LAUNCH(stream, debug);
+                cur ^= 1;
+                continue;
+            }
             SortPassFn kern; size_t smem;
             sort_pass_kernel(1, p, &kern, &smem);
             kern<<<(unsigned)sort_tiles, SORT_THREADS, smem, stream>>>(
@@ -1065,7 +1249,7 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
         count_launch();
         int rb = (int)((n_hint + 255) / 256);
         if (rb > 148 * 16) rb = 148 * 16;
-        tile_ranges_kernel<<<rb, 256, 0, stream>>>(bw.keys[cur], g.header, capacity, ranges);
+        tile_ranges_kernel<<<rb, 256, 0, stream>>>(bw.keys[cur], g.header, capacity, ranges, xy_keys, grid_x);
         B200S_AFTER_LAUNCH(stream, debug);
     }
     return 0;
