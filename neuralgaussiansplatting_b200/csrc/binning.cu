@@ -118,10 +118,22 @@ __device__ __forceinline__ T warp_lookback(const T* status, int64_t tile, B200sH
 }
 
 // Per-thread look-back (one chain per radix digit) with LB independent loads in flight per step.
+//
+// Rows of a pass's look-back array are laid out in groups: the LB_GROUP tile rows of group g, then ONE group row
+// (lb_phys / lb_group_row). Grouped mode (default): a tile first walks the predecessors inside its own group (at most
+// LB_GROUP - 1 words, one window), then the GROUP rows of earlier groups: sum of the group's tiles (published by the
+// group's last tile as soon as it has seen its in-group predecessors) or inclusive prefix through the group's end.
+// With ~450 tiles resident at once the flat walk visits ~100-150 predecessor words per tile in windows of 8 (a dozen
+// serialised L2 round trips and 37 % of the pass's executed instructions, ncu r02i); the grouped walk visits at most
+// LB_GROUP - 1 + tiles_in_flight / LB_GROUP.
 #ifndef B200S_LB_DEPTH
 #define B200S_LB_DEPTH 8
 #endif
 constexpr int LB_DEPTH = B200S_LB_DEPTH;
+constexpr int LBG_DEPTH = 16;
+__device__ __forceinline__ int64_t lb_phys(int64_t tile) { return tile + tile / LB_GROUP; }
+__device__ __forceinline__ int64_t lb_group_row(int64_t group) { return group * (LB_GROUP + 1) + LB_GROUP; }
+
 __device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t stride, int64_t tile, B200sHeader* header) {
     uint32_t excl = 0;
     int64_t t = tile - 1;
@@ -130,7 +142,7 @@ __device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t 
         uint32_t w[LB_DEPTH];
 #pragma unroll
         for (int i = 0; i < LB_DEPTH; ++i)
-            w[i] = (t - i >= 0) ? ld_volatile_u32(col + (size_t)(t - i) * stride) : FLAG_INCL;
+            w[i] = (t - i >= 0) ? ld_volatile_u32(col + (size_t)lb_phys(t - i) * stride) : FLAG_INCL;
         bool done = false, stop = false;
         int take = 0;
 #pragma unroll
@@ -148,6 +160,65 @@ __device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t 
             __nanosleep(20);
         }
     }
+    return excl;
+}
+
+// Walks the words at rows first, first - step, ... (`cnt` of them, nearest first), adding their values to `excl`.
+// Returns true when an inclusive word ended the walk (or on timeout), false when all cnt words were aggregates.
+__device__ __forceinline__ bool lookback_walk(const uint32_t* col, size_t stride, int64_t first, int64_t step, int64_t cnt,
+                                              uint32_t& excl, B200sHeader* header) {
+    int64_t k = 0;
+    int spins = 0;
+    while (k < cnt) {
+        uint32_t w[LBG_DEPTH];
+#pragma unroll
+        for (int i = 0; i < LBG_DEPTH; ++i)
+            w[i] = (k + i < cnt) ? ld_volatile_u32(col + (size_t)(first - (k + i) * step) * stride) : 0u;
+        bool done = false, stop = false;
+        int take = 0;
+#pragma unroll
+        for (int i = 0; i < LBG_DEPTH; ++i) {
+            if (!done && !stop && k + i < cnt) {
+                const uint32_t f = w[i] & 3u;
+                if (f == 0u) stop = true;
+                else { excl += w[i] >> 2; ++take; if (f == FLAG_INCL) done = true; }
+            }
+        }
+        if (done) return true;
+        k += take;
+        if (take == 0) {
+            if (++spins > SPIN_LIMIT) { atomicOr(&header->error, (uint32_t)ERR_LOOKBACK_TIMEOUT); return true; }
+            __nanosleep(20);
+        }
+    }
+    return false;
+}
+
+// Publishes this tile's digit count, finds its exclusive prefix and publishes the inclusive one; `col` = the
+// pass's look-back array + this thread's digit. Returns the exclusive prefix.
+__device__ __forceinline__ uint32_t lookback_exchange(uint32_t* col, size_t stride, int64_t tile, uint32_t count,
+                                                      bool already_published, int grouped, B200sHeader* header) {
+    uint32_t* mine = col + (size_t)lb_phys(tile) * stride;
+    if (!already_published) st_volatile_u32(mine, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
+    uint32_t excl = 0;
+    if (!grouped) {
+        if (tile != 0) {
+            excl = thread_lookback(col, stride, tile, header);
+            st_volatile_u32(mine, ((excl + count) << 2) | FLAG_INCL);
+        }
+        return excl;
+    }
+    const int64_t g = tile / LB_GROUP, in_group = tile - g * LB_GROUP;
+    const bool closer = in_group == LB_GROUP - 1;
+    uint32_t* grow = col + (size_t)lb_group_row(g) * stride;
+    // rows of a group are physically consecutive: predecessor i of this tile is row lb_phys(tile) - 1 - i
+    bool done = lookback_walk(col, stride, lb_phys(tile) - 1, 1, in_group, excl, header);
+    if (!done) {
+        if (closer && g != 0) st_volatile_u32(grow, ((excl + count) << 2) | FLAG_AGG);
+        if (g != 0) lookback_walk(col, stride, lb_group_row(g - 1), LB_GROUP + 1, g, excl, header);
+    }
+    if (tile != 0) st_volatile_u32(mine, ((excl + count) << 2) | FLAG_INCL);
+    if (closer) st_volatile_u32(grow, ((excl + count) << 2) | FLAG_INCL);
     return excl;
 }
 
@@ -314,6 +385,9 @@ sort_scan_hist_kernel(uint32_t* hist, int from_diff) {
 #ifndef B200S_XY_KEYS_DEFAULT
 #define B200S_XY_KEYS_DEFAULT 0
 #endif
+#ifndef B200S_LB_GROUPED_DEFAULT
+#define B200S_LB_GROUPED_DEFAULT 1
+#endif
 #ifndef B200S_FUSE_EXPAND_DEFAULT
 #define B200S_FUSE_EXPAND_DEFAULT 0
 #endif
@@ -331,7 +405,7 @@ __global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
 sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                      B200sHeader* header, const uint32_t* __restrict__ n_ptr, int64_t capacity, int shift,
-                     const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket) {
+                     const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket, int lb_grouped) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* s_keys = reinterpret_cast<uint32_t*>(smem_raw);
     uint32_t* s_vals = s_keys + SORT_TILE;
@@ -422,8 +496,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
 
     // Publish this tile's digit counts first, scatter locally while the predecessors make progress, and only then
     // look back: key / val / dr registers are dead by then, so the look-back can keep LB_DEPTH loads in flight.
-    uint32_t* lb = lookback + (size_t)tile * SORT_RADIX + tid;
-    st_volatile_u32(lb, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
+    st_volatile_u32(lookback + (size_t)lb_phys(tile) * SORT_RADIX + tid, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
     s_dstart[tid] = dstart;
     __syncthreads();
 
@@ -436,11 +509,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         s_keys[pos] = key[k];
         s_vals[pos] = val[k];
     }
-    uint32_t excl = 0;
-    if (tile != 0) {
-        excl = thread_lookback(lookback + tid, SORT_RADIX, (int64_t)tile, header);
-        st_volatile_u32(lb, ((excl + count) << 2) | FLAG_INCL);
-    }
+    const uint32_t excl = lookback_exchange(lookback + tid, SORT_RADIX, (int64_t)tile, count, true, lb_grouped, header);
     s_gbase[tid] = bin_base[tid] + excl - dstart;
     __syncthreads();
     for (uint32_t i = tid; i < tile_n; i += SORT_THREADS) {
@@ -593,7 +662,7 @@ __device__ __forceinline__ void cr_sort_tile(uint32_t (&key)[SORT_ITEMS], uint32
 __device__ __forceinline__ void cr_scatter_tile(const CrSmem& sm, uint32_t tile, uint32_t tile_n, uint32_t n, int shift,
                                                 const uint32_t* __restrict__ bin_base, uint32_t* lookback,
                                                 B200sHeader* header, uint32_t* __restrict__ keys_out,
-                                                uint32_t* __restrict__ vals_out) {
+                                                uint32_t* __restrict__ vals_out, int lb_grouped) {
     const int tid = threadIdx.x;
     {
         const uint32_t d = (uint32_t)tid;
@@ -609,13 +678,7 @@ __device__ __forceinline__ void cr_scatter_tile(const CrSmem& sm, uint32_t tile,
     __syncthreads();
     const uint32_t dstart = sm.dstart[tid];
     const uint32_t count = sm.dstart[tid + 1] - dstart;
-    uint32_t* lb = lookback + (size_t)tile * SORT_RADIX + tid;
-    st_volatile_u32(lb, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
-    uint32_t excl = 0;
-    if (tile != 0) {
-        excl = thread_lookback(lookback + tid, SORT_RADIX, (int64_t)tile, header);
-        st_volatile_u32(lb, ((excl + count) << 2) | FLAG_INCL);
-    }
+    const uint32_t excl = lookback_exchange(lookback + tid, SORT_RADIX, (int64_t)tile, count, false, lb_grouped, header);
     sm.gbase[tid] = bin_base[tid] + excl - dstart;
     __syncthreads();
     for (uint32_t i = tid; i < tile_n; i += SORT_THREADS) {
@@ -633,7 +696,7 @@ __global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
 sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                            uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                            B200sHeader* header, const uint32_t* __restrict__ n_ptr, int64_t capacity, int shift,
-                           const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket) {
+                           const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket, int lb_grouped) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const CrSmem sm = cr_carve(smem_raw, smem_raw + CR_ARRAY_BYTES);
     const int tid = threadIdx.x;
@@ -671,7 +734,7 @@ sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t*
         }
     }
     cr_sort_tile(key, val, sm, shift);
-    cr_scatter_tile(sm, tile, tile_n, n, shift, bin_base, lookback, header, keys_out, vals_out);
+    cr_scatter_tile(sm, tile, tile_n, n, shift, bin_base, lookback, header, keys_out, vals_out, lb_grouped);
 }
 
 // ----------------------------------------------------------------------------- expand
@@ -899,7 +962,7 @@ expand_sort_count_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t
                          const uint32_t* __restrict__ run_rmin, const uint32_t* __restrict__ run_rwh,
                          const uint32_t* __restrict__ block_first, uint32_t* __restrict__ keys_out,
                          uint32_t* __restrict__ vals_out, B200sHeader* header, int64_t capacity,
-                         const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket) {
+                         const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket, int lb_grouped) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* s_end = reinterpret_cast<uint32_t*>(smem_raw);
     unsigned char* uni = smem_raw + XP_RUN_BYTES;                   // run arrays first, the sort's arrays afterwards
@@ -966,7 +1029,7 @@ expand_sort_count_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t
     }
     __syncthreads();                                                // the run arrays are dead: their space is the sort's
     cr_sort_tile(key, val, sm, 0);
-    cr_scatter_tile(sm, tile, tile_n, n, 0, bin_base, lookback, header, keys_out, vals_out);
+    cr_scatter_tile(sm, tile, tile_n, n, 0, bin_base, lookback, header, keys_out, vals_out, lb_grouped);
 }
 
 // ----------------------------------------------------------------------------- ranges
@@ -1116,7 +1179,11 @@ static int set_sort_attr() {
     return 0;
 }
 using SortPassFn = void (*)(const uint32_t*, const uint32_t*, uint32_t*, uint32_t*, B200sHeader*, const uint32_t*, int64_t,
-                            int, const uint32_t*, uint32_t*, uint32_t*);
+                            int, const uint32_t*, uint32_t*, uint32_t*, int);
+static int lb_grouped_mode() {
+    static int v = [] { const char* e = getenv("B200S_LB_GROUPED"); return e && *e ? atoi(e) : B200S_LB_GROUPED_DEFAULT; }();
+    return v;
+}
 static void sort_pass_kernel(int which, int pass, SortPassFn* fn, size_t* smem) {
     if (rank_by_count(which, pass)) { *fn = sort_onesweep_count_kernel; *smem = SORT_CR_SMEM; }
     else { *fn = rank_by_match(which, pass) ? sort_onesweep_kernel<true> : sort_onesweep_kernel<false>; *smem = SORT_SMEM; }
@@ -1154,7 +1221,8 @@ int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t 
             kern<<<(unsigned)g.depth_tiles, SORT_THREADS, smem, stream>>>(
                 g.vis_keys[cur], g.vis_ids[cur], g.vis_keys[cur ^ 1], g.vis_ids[cur ^ 1], g.header, n_ptr,
                 (int64_t)P, p * SORT_RADIX_BITS, g.depth_hist + p * SORT_RADIX,
-                g.depth_lookback + (size_t)p * g.depth_tiles * SORT_RADIX, g.counters + CTR_DEPTH_TICKET0 + p);
+                g.depth_lookback + (size_t)p * lb_rows(g.depth_tiles) * SORT_RADIX, g.counters + CTR_DEPTH_TICKET0 + p,
+                lb_grouped_mode());
             B200S_AFTER_LAUNCH(stream, debug);
             cur ^= 1;
         }
@@ -1228,7 +1296,7 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
             if (p == 0 && fuse_expand && P > 0) {
                 expand_sort_count_kernel<<<(unsigned)sort_tiles, SORT_THREADS, SORT_XP_SMEM, stream>>>(
                     g.vis_ids[0], g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, bw.keys[1], bw.vals[1],
-                    g.header, capacity, bw.hist, bw.lookback, g.counters + CTR_SORT_TICKET0);
+                    g.header, capacity, bw.hist, bw.lookback, g.counters + CTR_SORT_TICKET0, lb_grouped_mode());
                 B200S_AFTER_LAUNCH(stream, debug);
                 cur ^= 1;
                 continue;
@@ -1238,7 +1306,8 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
             kern<<<(unsigned)sort_tiles, SORT_THREADS, smem, stream>>>(
                 bw.keys[cur], bw.vals[cur], bw.keys[cur ^ 1], bw.vals[cur ^ 1], g.header, &g.header->num_rendered,
                 capacity, p * SORT_RADIX_BITS, bw.hist + p * SORT_RADIX,
-                bw.lookback + (size_t)p * bw.sort_tiles * SORT_RADIX, g.counters + CTR_SORT_TICKET0 + p);
+                bw.lookback + (size_t)p * lb_rows(bw.sort_tiles) * SORT_RADIX, g.counters + CTR_SORT_TICKET0 + p,
+                lb_grouped_mode());
             B200S_AFTER_LAUNCH(stream, debug);
             cur ^= 1;
         }

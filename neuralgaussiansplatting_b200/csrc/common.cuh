@@ -59,6 +59,10 @@ constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 16;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
+// Look-back rows of a sort pass: the tile rows in groups of LB_GROUP, each group followed by one group row
+// (binning.cu: lookback_exchange).
+constexpr int LB_GROUP = 16;
+inline int64_t lb_rows(int64_t tiles) { return tiles + (tiles + LB_GROUP - 1) / LB_GROUP; }
 constexpr int SORT_MAX_PASSES = 4;    // onesweep passes over the tile bits (<= 32 bits of tile id)
 constexpr int DEPTH_PASSES = 4;       // onesweep passes over the 32 depth bits
 
@@ -81,7 +85,7 @@ struct GeomWS {
     uint32_t* vis_ids[2];     // [P] their Gaussian ids; after the depth sort: front-to-back order
     unsigned long long* scan_status;   // [ceil(P / SCAN_TILE) + 1] decoupled look-back words
     uint32_t* depth_hist;     // [DEPTH_PASSES][SORT_RADIX]
-    uint32_t* depth_lookback; // [DEPTH_PASSES][ceil(P / SORT_TILE)][SORT_RADIX]
+    uint32_t* depth_lookback; // [DEPTH_PASSES][lb_rows(ceil(P / SORT_TILE))][SORT_RADIX]
     uint32_t* exp_status;     // [ceil(P / EXP_TILE) + 1] look-back words of the expansion
     size_t zero_off, zero_bytes;   // scan_status..exp_status are contiguous: cleared every call
     int64_t depth_tiles;
@@ -108,7 +112,7 @@ inline GeomWS carve_geom(void* base, int64_t P) {
     g.zero_off = off;
     g.scan_status = (unsigned long long*)take(8 * ((size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1));
     g.depth_hist = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * SORT_RADIX);
-    g.depth_lookback = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * g.depth_tiles * SORT_RADIX);
+    g.depth_lookback = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * lb_rows(g.depth_tiles) * SORT_RADIX);
     g.exp_status = (uint32_t*)take(4 * ((size_t)(P + EXP_TILE - 1) / EXP_TILE + 1));
     g.zero_bytes = off - g.zero_off;
     g.bytes = off;
@@ -146,7 +150,7 @@ struct BinWS {
     uint32_t* keys[2];     // [capacity] tile id of every instance (ping-pong)
     uint32_t* vals[2];     // [capacity] Gaussian id of every instance
     uint32_t* hist;        // [SORT_MAX_PASSES][SORT_RADIX] digit histograms -> exclusive bases
-    uint32_t* lookback;    // [SORT_MAX_PASSES][sort_tiles][SORT_RADIX]
+    uint32_t* lookback;    // [SORT_MAX_PASSES][lb_rows(sort_tiles)][SORT_RADIX]
     uint32_t* block_first; // [capacity / EXP_OUT_TILE + 2] first Gaussian of every expansion block
     size_t zero_bytes;     // hist+lookback are contiguous: bytes to clear before a sort
     int64_t sort_tiles;
@@ -166,7 +170,7 @@ inline BinWS carve_bin(void* base, int64_t capacity) {
     s.vals[1] = (uint32_t*)take(4 * (size_t)capacity);
     size_t z0 = off;
     s.hist = (uint32_t*)take(4 * (size_t)SORT_MAX_PASSES * SORT_RADIX);
-    s.lookback = (uint32_t*)take(4 * (size_t)SORT_MAX_PASSES * s.sort_tiles * SORT_RADIX);
+    s.lookback = (uint32_t*)take(4 * (size_t)SORT_MAX_PASSES * lb_rows(s.sort_tiles) * SORT_RADIX);
     s.zero_bytes = off - z0;
     s.block_first = (uint32_t*)take(4 * ((size_t)capacity / EXP_OUT_TILE + 2));
     s.bytes = off;
