@@ -119,21 +119,16 @@ __device__ __forceinline__ T warp_lookback(const T* status, int64_t tile, B200sH
 
 // Per-thread look-back (one chain per radix digit) with LB independent loads in flight per step.
 //
-// Rows of a pass's look-back array are laid out in groups: the LB_GROUP tile rows of group g, then ONE group row
-// (lb_phys / lb_group_row). Grouped mode (default): a tile first walks the predecessors inside its own group (at most
-// LB_GROUP - 1 words, one window), then the GROUP rows of earlier groups: sum of the group's tiles (published by the
-// group's last tile as soon as it has seen its in-group predecessors) or inclusive prefix through the group's end.
-// With ~450 tiles resident at once the flat walk visits ~100-150 predecessor words per tile in windows of 8 (a dozen
-// serialised L2 round trips and 37 % of the pass's executed instructions, ncu r02i); the grouped walk visits at most
-// LB_GROUP - 1 + tiles_in_flight / LB_GROUP.
+// Measured and rejected (round 2, profiles/r02j_*): a GROUPED look-back (one extra row per 16 tiles holding the
+// group's sum / inclusive prefix, so that a tile walks <= 15 in-group words + one word per earlier group instead of
+// the ~100-150 words of the flat walk). The protocol is correct (bit-exact suite green) but slower: C3 sort 0.278 ->
+// 0.317 ms, C4 0.516 -> 0.608 ms. A group's row only appears when its last tile has reached its own look-back, so
+// later tiles WAIT on the progress of their neighbours; the flat walk never waits for progress, only for counts that
+// every resident tile publishes right after ranking.
 #ifndef B200S_LB_DEPTH
 #define B200S_LB_DEPTH 8
 #endif
 constexpr int LB_DEPTH = B200S_LB_DEPTH;
-constexpr int LBG_DEPTH = 16;
-__device__ __forceinline__ int64_t lb_phys(int64_t tile) { return tile + tile / LB_GROUP; }
-__device__ __forceinline__ int64_t lb_group_row(int64_t group) { return group * (LB_GROUP + 1) + LB_GROUP; }
-
 __device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t stride, int64_t tile, B200sHeader* header) {
     uint32_t excl = 0;
     int64_t t = tile - 1;
@@ -142,7 +137,7 @@ __device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t 
         uint32_t w[LB_DEPTH];
 #pragma unroll
         for (int i = 0; i < LB_DEPTH; ++i)
-            w[i] = (t - i >= 0) ? ld_volatile_u32(col + (size_t)lb_phys(t - i) * stride) : FLAG_INCL;
+            w[i] = (t - i >= 0) ? ld_volatile_u32(col + (size_t)(t - i) * stride) : FLAG_INCL;
         bool done = false, stop = false;
         int take = 0;
 #pragma unroll
@@ -163,62 +158,17 @@ __device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t 
     return excl;
 }
 
-// Walks the words at rows first, first - step, ... (`cnt` of them, nearest first), adding their values to `excl`.
-// Returns true when an inclusive word ended the walk (or on timeout), false when all cnt words were aggregates.
-__device__ __forceinline__ bool lookback_walk(const uint32_t* col, size_t stride, int64_t first, int64_t step, int64_t cnt,
-                                              uint32_t& excl, B200sHeader* header) {
-    int64_t k = 0;
-    int spins = 0;
-    while (k < cnt) {
-        uint32_t w[LBG_DEPTH];
-#pragma unroll
-        for (int i = 0; i < LBG_DEPTH; ++i)
-            w[i] = (k + i < cnt) ? ld_volatile_u32(col + (size_t)(first - (k + i) * step) * stride) : 0u;
-        bool done = false, stop = false;
-        int take = 0;
-#pragma unroll
-        for (int i = 0; i < LBG_DEPTH; ++i) {
-            if (!done && !stop && k + i < cnt) {
-                const uint32_t f = w[i] & 3u;
-                if (f == 0u) stop = true;
-                else { excl += w[i] >> 2; ++take; if (f == FLAG_INCL) done = true; }
-            }
-        }
-        if (done) return true;
-        k += take;
-        if (take == 0) {
-            if (++spins > SPIN_LIMIT) { atomicOr(&header->error, (uint32_t)ERR_LOOKBACK_TIMEOUT); return true; }
-            __nanosleep(20);
-        }
-    }
-    return false;
-}
-
-// Publishes this tile's digit count, finds its exclusive prefix and publishes the inclusive one; `col` = the
-// pass's look-back array + this thread's digit. Returns the exclusive prefix.
+// Publishes this tile's digit count (unless the caller already has), finds its exclusive prefix and publishes the
+// inclusive one; `col` = the pass's look-back array + this thread's digit. Returns the exclusive prefix.
 __device__ __forceinline__ uint32_t lookback_exchange(uint32_t* col, size_t stride, int64_t tile, uint32_t count,
-                                                      bool already_published, int grouped, B200sHeader* header) {
-    uint32_t* mine = col + (size_t)lb_phys(tile) * stride;
+                                                      bool already_published, B200sHeader* header) {
+    uint32_t* mine = col + (size_t)tile * stride;
     if (!already_published) st_volatile_u32(mine, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
     uint32_t excl = 0;
-    if (!grouped) {
-        if (tile != 0) {
-            excl = thread_lookback(col, stride, tile, header);
-            st_volatile_u32(mine, ((excl + count) << 2) | FLAG_INCL);
-        }
-        return excl;
+    if (tile != 0) {
+        excl = thread_lookback(col, stride, tile, header);
+        st_volatile_u32(mine, ((excl + count) << 2) | FLAG_INCL);
     }
-    const int64_t g = tile / LB_GROUP, in_group = tile - g * LB_GROUP;
-    const bool closer = in_group == LB_GROUP - 1;
-    uint32_t* grow = col + (size_t)lb_group_row(g) * stride;
-    // rows of a group are physically consecutive: predecessor i of this tile is row lb_phys(tile) - 1 - i
-    bool done = lookback_walk(col, stride, lb_phys(tile) - 1, 1, in_group, excl, header);
-    if (!done) {
-        if (closer && g != 0) st_volatile_u32(grow, ((excl + count) << 2) | FLAG_AGG);
-        if (g != 0) lookback_walk(col, stride, lb_group_row(g - 1), LB_GROUP + 1, g, excl, header);
-    }
-    if (tile != 0) st_volatile_u32(mine, ((excl + count) << 2) | FLAG_INCL);
-    if (closer) st_volatile_u32(grow, ((excl + count) << 2) | FLAG_INCL);
     return excl;
 }
 
@@ -318,6 +268,118 @@ scan_compact_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict_
     }
 }
 
+// ------------------------------------------------------------------- chain-free scans
+// The two prefix sums of the binning (tiles_touched in Gaussian-index order; instance counts in depth order) run
+// over 12-24 MB: at that size a chained look-back is LATENCY bound (scan_compact 35 us, sorted_scan 47 us at C3 for
+// ~5 us of HBM time, ncu r02i: issue slots 9 % busy). Chain-free form: the producing kernel leaves one partial sum per
+// block (preprocess_fwd: per 256 Gaussians; run_gather: per EXP_TILE depth-sorted Gaussians), ONE block scans the
+// partials, and the consumer applies the prefix of its first block — no tickets, no spinning, no status words.
+constexpr int SP_THREADS = 1024;
+__global__ void __launch_bounds__(SP_THREADS)
+scan_partials_kernel(const unsigned long long* __restrict__ sums, unsigned long long* __restrict__ prefix, int n,
+                     B200sHeader* header, int publish) {
+    __shared__ unsigned long long s_warp[SP_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (n + SP_THREADS - 1) / SP_THREADS;
+    const int i0 = min(n, tid * per), i1 = min(n, i0 + per);
+    unsigned long long mine = 0;
+    for (int i = i0; i < i1; ++i) mine += sums[i];
+    unsigned long long incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long t = __shfl_up_sync(FULL_MASK, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    unsigned long long wex = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < SP_THREADS / 32; ++w) {
+        const unsigned long long t = s_warp[w];
+        if (w < warp) wex += t;
+        total += t;
+    }
+    unsigned long long run = wex + incl - mine;
+    for (int i = i0; i < i1; ++i) {
+        prefix[i] = run;
+        run += sums[i];
+    }
+    if (publish && tid == 0) {
+        header->num_rendered = (uint32_t)total;            // sum of tiles_touched (< 2^32, as in the chained scan)
+        header->num_visible = (uint32_t)(total >> 32);
+    }
+}
+
+// scan_compact_kernel without the chain: the exclusive prefix of a tile is pre_prefix of its first preprocess block.
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_apply_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict__ depth_bits,
+                  uint32_t* __restrict__ out, uint32_t* __restrict__ vis_keys, uint32_t* __restrict__ vis_ids,
+                  int P, const unsigned long long* __restrict__ pre_prefix) {
+    __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t tile = blockIdx.x;
+    const int64_t base = (int64_t)tile * SCAN_TILE + (int64_t)tid * SCAN_ITEMS;
+
+    uint32_t v[SCAN_ITEMS], dep[SCAN_ITEMS];
+    if (base + SCAN_ITEMS <= P) {
+        const uint4* src = reinterpret_cast<const uint4*>(in + base);
+        const uint4* dsrc = reinterpret_cast<const uint4*>(depth_bits + base);
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS / 4; ++i) {
+            const uint4 t = src[i];
+            v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+            const uint4 d = dsrc[i];
+            dep[4 * i] = d.x; dep[4 * i + 1] = d.y; dep[4 * i + 2] = d.z; dep[4 * i + 3] = d.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; ++i) {
+            v[i] = (base + i < P) ? in[base + i] : 0u;
+            dep[i] = (base + i < P) ? depth_bits[base + i] : 0u;
+        }
+    }
+    uint32_t tsum = 0, vmask = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+        if (v[i] != 0u) vmask |= 1u << i;
+        tsum += v[i]; v[i] = tsum;                     // thread-inclusive
+    }
+    const unsigned long long mine = (unsigned long long)tsum | ((unsigned long long)__popc(vmask) << 32);
+    unsigned long long incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long t = __shfl_up_sync(FULL_MASK, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    unsigned long long warp_excl = 0;
+#pragma unroll
+    for (int w = 0; w < SCAN_THREADS / 32; ++w)
+        if (w < warp) warp_excl += s_warp[w];
+    const unsigned long long pre = pre_prefix[(size_t)tile * (SCAN_TILE / PRE_BLOCK)] + warp_excl + (incl - mine);
+    const uint32_t off = (uint32_t)pre;
+    uint32_t ci = (uint32_t)(pre >> 32);
+    if (base + SCAN_ITEMS <= P) {
+        uint4* dst = reinterpret_cast<uint4*>(out + base);
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS / 4; ++i)
+            dst[i] = make_uint4(v[4 * i] + off, v[4 * i + 1] + off, v[4 * i + 2] + off, v[4 * i + 3] + off);
+    } else {
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; ++i)
+            if (base + i < P) out[base + i] = v[i] + off;
+    }
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+        if ((vmask >> i) & 1u) {
+            vis_keys[ci] = dep[i];
+            vis_ids[ci] = (uint32_t)(base + i);
+            ++ci;
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------- sort
 // Digit histograms of all passes in one read of the keys (used for the depth sort; the tile
 // sort's histogram is accumulated by the expansion kernel).
@@ -385,8 +447,8 @@ sort_scan_hist_kernel(uint32_t* hist, int from_diff) {
 #ifndef B200S_XY_KEYS_DEFAULT
 #define B200S_XY_KEYS_DEFAULT 0
 #endif
-#ifndef B200S_LB_GROUPED_DEFAULT
-#define B200S_LB_GROUPED_DEFAULT 1
+#ifndef B200S_CHAINFREE_DEFAULT
+#define B200S_CHAINFREE_DEFAULT 0
 #endif
 #ifndef B200S_FUSE_EXPAND_DEFAULT
 #define B200S_FUSE_EXPAND_DEFAULT 0
@@ -405,7 +467,7 @@ __global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
 sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                      B200sHeader* header, const uint32_t* __restrict__ n_ptr, int64_t capacity, int shift,
-                     const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket, int lb_grouped) {
+                     const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* s_keys = reinterpret_cast<uint32_t*>(smem_raw);
     uint32_t* s_vals = s_keys + SORT_TILE;
@@ -496,7 +558,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
 
     // Publish this tile's digit counts first, scatter locally while the predecessors make progress, and only then
     // look back: key / val / dr registers are dead by then, so the look-back can keep LB_DEPTH loads in flight.
-    st_volatile_u32(lookback + (size_t)lb_phys(tile) * SORT_RADIX + tid, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
+    st_volatile_u32(lookback + (size_t)tile * SORT_RADIX + tid, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
     s_dstart[tid] = dstart;
     __syncthreads();
 
@@ -509,7 +571,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         s_keys[pos] = key[k];
         s_vals[pos] = val[k];
     }
-    const uint32_t excl = lookback_exchange(lookback + tid, SORT_RADIX, (int64_t)tile, count, true, lb_grouped, header);
+    const uint32_t excl = lookback_exchange(lookback + tid, SORT_RADIX, (int64_t)tile, count, true, header);
     s_gbase[tid] = bin_base[tid] + excl - dstart;
     __syncthreads();
     for (uint32_t i = tid; i < tile_n; i += SORT_THREADS) {
@@ -662,7 +724,7 @@ __device__ __forceinline__ void cr_sort_tile(uint32_t (&key)[SORT_ITEMS], uint32
 __device__ __forceinline__ void cr_scatter_tile(const CrSmem& sm, uint32_t tile, uint32_t tile_n, uint32_t n, int shift,
                                                 const uint32_t* __restrict__ bin_base, uint32_t* lookback,
                                                 B200sHeader* header, uint32_t* __restrict__ keys_out,
-                                                uint32_t* __restrict__ vals_out, int lb_grouped) {
+                                                uint32_t* __restrict__ vals_out) {
     const int tid = threadIdx.x;
     {
         const uint32_t d = (uint32_t)tid;
@@ -678,7 +740,7 @@ __device__ __forceinline__ void cr_scatter_tile(const CrSmem& sm, uint32_t tile,
     __syncthreads();
     const uint32_t dstart = sm.dstart[tid];
     const uint32_t count = sm.dstart[tid + 1] - dstart;
-    const uint32_t excl = lookback_exchange(lookback + tid, SORT_RADIX, (int64_t)tile, count, false, lb_grouped, header);
+    const uint32_t excl = lookback_exchange(lookback + tid, SORT_RADIX, (int64_t)tile, count, false, header);
     sm.gbase[tid] = bin_base[tid] + excl - dstart;
     __syncthreads();
     for (uint32_t i = tid; i < tile_n; i += SORT_THREADS) {
@@ -696,7 +758,7 @@ __global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
 sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                            uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                            B200sHeader* header, const uint32_t* __restrict__ n_ptr, int64_t capacity, int shift,
-                           const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket, int lb_grouped) {
+                           const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const CrSmem sm = cr_carve(smem_raw, smem_raw + CR_ARRAY_BYTES);
     const int tid = threadIdx.x;
@@ -734,7 +796,7 @@ sort_onesweep_count_kernel(const uint32_t* __restrict__ keys_in, const uint32_t*
         }
     }
     cr_sort_tile(key, val, sm, shift);
-    cr_scatter_tile(sm, tile, tile_n, n, shift, bin_base, lookback, header, keys_out, vals_out, lb_grouped);
+    cr_scatter_tile(sm, tile, tile_n, n, shift, bin_base, lookback, header, keys_out, vals_out);
 }
 
 // ----------------------------------------------------------------------------- expand
@@ -840,6 +902,108 @@ sorted_scan_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __re
         for (int i = tid; i < 2 * SORT_RADIX; i += SS_THREADS) {
             const uint32_t c = s_diff[i];
             if (c) atomicAdd(&hist[i], c);
+        }
+    }
+}
+
+// sorted_scan_kernel without the chain, in two kernels around scan_partials_kernel:
+// run_gather: the rectangle of every depth-sorted Gaussian as dense arrays + the instance count of every block
+// (+ the (x, y) digit histograms as range-adds); run_apply: block-local scan + the block's prefix -> run_end, block_first.
+__global__ void __launch_bounds__(SS_THREADS)
+run_gather_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __restrict__ rec,
+                  uint32_t* __restrict__ run_rmin, uint32_t* __restrict__ run_rwh,
+                  unsigned long long* __restrict__ run_sums, B200sHeader* header, int64_t capacity,
+                  uint32_t* __restrict__ hist, int xy_keys) {
+    __shared__ uint32_t s_warp[SS_THREADS / 32];
+    __shared__ uint32_t s_diff[2 * SORT_RADIX];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t n_vis = header->num_visible;
+    const bool overflow = (int64_t)header->num_rendered > capacity;
+    if (overflow && blockIdx.x == 0 && tid == 0) header->overflow = 1u;
+    if (xy_keys) for (int i = tid; i < 2 * SORT_RADIX; i += SS_THREADS) s_diff[i] = 0u;
+    __syncthreads();
+    const uint32_t g0 = blockIdx.x * EXP_TILE + tid * EXP_ITEMS;
+    uint32_t tsum = 0;
+    if (!overflow) {
+#pragma unroll
+        for (int k = 0; k < EXP_ITEMS; ++k) {
+            if (g0 + k < n_vis) {
+                const float4 q2 = rec[sorted_ids[g0 + k]].q2;
+                const uint32_t rmin = __float_as_uint(q2.z), rwh = __float_as_uint(q2.w);
+                const uint32_t w = rwh & 0xffffu, h = rwh >> 16;
+                run_rmin[g0 + k] = rmin;
+                run_rwh[g0 + k] = rwh;
+                tsum += w * h;
+                if (xy_keys && w * h != 0u) {
+                    const uint32_t x0 = rmin & 0xffffu, y0 = rmin >> 16;
+                    B200S_CHECK(x0 + w <= (uint32_t)SORT_RADIX && y0 + h <= (uint32_t)SORT_RADIX);
+                    atomicAdd(&s_diff[x0], h);
+                    if (x0 + w < (uint32_t)SORT_RADIX) atomicAdd(&s_diff[x0 + w], 0u - h);
+                    atomicAdd(&s_diff[SORT_RADIX + y0], w);
+                    if (y0 + h < (uint32_t)SORT_RADIX) atomicAdd(&s_diff[SORT_RADIX + y0 + h], 0u - w);
+                }
+            }
+        }
+    }
+    const uint32_t wsum = __reduce_add_sync(FULL_MASK, tsum);
+    if (lane == 0) s_warp[warp] = wsum;
+    __syncthreads();
+    if (tid == 0) {
+        unsigned long long tot = 0;
+#pragma unroll
+        for (int w = 0; w < SS_THREADS / 32; ++w) tot += s_warp[w];
+        run_sums[blockIdx.x] = tot;
+    }
+    if (xy_keys && !overflow) {
+        for (int i = tid; i < 2 * SORT_RADIX; i += SS_THREADS) {
+            const uint32_t c = s_diff[i];
+            if (c) atomicAdd(&hist[i], c);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(SS_THREADS)
+run_apply_kernel(const uint32_t* __restrict__ run_rwh, const unsigned long long* __restrict__ run_prefix,
+                 uint32_t* __restrict__ run_end, uint32_t* __restrict__ block_first, const B200sHeader* header,
+                 int64_t capacity) {
+    __shared__ uint32_t s_warp[SS_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t n_vis = header->num_visible;
+    if ((int64_t)header->num_rendered > capacity) return;
+    const uint32_t g0 = blockIdx.x * EXP_TILE + tid * EXP_ITEMS;
+    if (blockIdx.x * (uint32_t)EXP_TILE >= n_vis) return;
+    uint32_t cnt[EXP_ITEMS];
+    uint32_t tsum = 0;
+#pragma unroll
+    for (int k = 0; k < EXP_ITEMS; ++k) {
+        cnt[k] = 0;
+        if (g0 + k < n_vis) {
+            const uint32_t rwh = run_rwh[g0 + k];
+            cnt[k] = (rwh & 0xffffu) * (rwh >> 16);
+        }
+        tsum += cnt[k];
+    }
+    uint32_t incl = tsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULL_MASK, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t wex = 0;
+#pragma unroll
+    for (int w = 0; w < SS_THREADS / 32; ++w)
+        if (w < warp) wex += s_warp[w];
+    uint32_t run = (uint32_t)run_prefix[blockIdx.x] + wex + incl - tsum;     // global start of this thread's first run
+#pragma unroll
+    for (int k = 0; k < EXP_ITEMS; ++k) {
+        if (g0 + k < n_vis) {
+            const uint32_t start = run, end = run + cnt[k];
+            run_end[g0 + k] = end;
+            for (uint32_t m = (start + OUT_TILE - 1) / OUT_TILE; (uint64_t)m * OUT_TILE < end; ++m)
+                block_first[m] = g0 + k;
+            run = end;
         }
     }
 }
@@ -962,7 +1126,7 @@ expand_sort_count_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t
                          const uint32_t* __restrict__ run_rmin, const uint32_t* __restrict__ run_rwh,
                          const uint32_t* __restrict__ block_first, uint32_t* __restrict__ keys_out,
                          uint32_t* __restrict__ vals_out, B200sHeader* header, int64_t capacity,
-                         const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket, int lb_grouped) {
+                         const uint32_t* __restrict__ bin_base, uint32_t* lookback, uint32_t* ticket) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* s_end = reinterpret_cast<uint32_t*>(smem_raw);
     unsigned char* uni = smem_raw + XP_RUN_BYTES;                   // run arrays first, the sort's arrays afterwards
@@ -1029,7 +1193,7 @@ expand_sort_count_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t
     }
     __syncthreads();                                                // the run arrays are dead: their space is the sort's
     cr_sort_tile(key, val, sm, 0);
-    cr_scatter_tile(sm, tile, tile_n, n, 0, bin_base, lookback, header, keys_out, vals_out, lb_grouped);
+    cr_scatter_tile(sm, tile, tile_n, n, 0, bin_base, lookback, header, keys_out, vals_out);
 }
 
 // ----------------------------------------------------------------------------- ranges
@@ -1179,9 +1343,9 @@ static int set_sort_attr() {
     return 0;
 }
 using SortPassFn = void (*)(const uint32_t*, const uint32_t*, uint32_t*, uint32_t*, B200sHeader*, const uint32_t*, int64_t,
-                            int, const uint32_t*, uint32_t*, uint32_t*, int);
-static int lb_grouped_mode() {
-    static int v = [] { const char* e = getenv("B200S_LB_GROUPED"); return e && *e ? atoi(e) : B200S_LB_GROUPED_DEFAULT; }();
+                            int, const uint32_t*, uint32_t*, uint32_t*);
+static int chainfree_mode() {
+    static int v = [] { const char* e = getenv("B200S_CHAINFREE"); return e && *e ? atoi(e) : B200S_CHAINFREE_DEFAULT; }();
     return v;
 }
 static void sort_pass_kernel(int which, int pass, SortPassFn* fn, size_t* smem) {
@@ -1197,10 +1361,19 @@ int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t 
     {
         ProfScope ps(B200S_STAGE_SCAN, stream);
         const int tiles = (P + SCAN_TILE - 1) / SCAN_TILE;
-        count_launch();
-        scan_compact_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(g.tiles_touched, g.depth_bits, g.point_offsets,
-                                                               g.vis_keys[0], g.vis_ids[0], P, g.scan_status,
-                                                               g.counters, g.header);
+        if (chainfree_mode()) {
+            count_launch(2);
+            scan_partials_kernel<<<1, SP_THREADS, 0, stream>>>(g.pre_sums, g.pre_prefix, (P + PRE_BLOCK - 1) / PRE_BLOCK,
+                                                              g.header, 1);
+            B200S_AFTER_LAUNCH(stream, debug);
+            scan_apply_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(g.tiles_touched, g.depth_bits, g.point_offsets,
+                                                                 g.vis_keys[0], g.vis_ids[0], P, g.pre_prefix);
+        } else {
+            count_launch();
+            scan_compact_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(g.tiles_touched, g.depth_bits, g.point_offsets,
+                                                                   g.vis_keys[0], g.vis_ids[0], P, g.scan_status,
+                                                                   g.counters, g.header);
+        }
         B200S_AFTER_LAUNCH(stream, debug);
     }
     {
@@ -1221,8 +1394,7 @@ int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t 
             kern<<<(unsigned)g.depth_tiles, SORT_THREADS, smem, stream>>>(
                 g.vis_keys[cur], g.vis_ids[cur], g.vis_keys[cur ^ 1], g.vis_ids[cur ^ 1], g.header, n_ptr,
                 (int64_t)P, p * SORT_RADIX_BITS, g.depth_hist + p * SORT_RADIX,
-                g.depth_lookback + (size_t)p * lb_rows(g.depth_tiles) * SORT_RADIX, g.counters + CTR_DEPTH_TICKET0 + p,
-                lb_grouped_mode());
+                g.depth_lookback + (size_t)p * g.depth_tiles * SORT_RADIX, g.counters + CTR_DEPTH_TICKET0 + p);
             B200S_AFTER_LAUNCH(stream, debug);
             cur ^= 1;
         }
@@ -1273,9 +1445,21 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
         // the depth sort's spare buffers (and its no longer needed sorted keys) hold the runs
         ProfScope ps(B200S_STAGE_EXPAND, stream);
         count_launch(2);
-        sorted_scan_kernel<<<(P + EXP_TILE - 1) / EXP_TILE, SS_THREADS, 0, stream>>>(
-            g.vis_ids[0], g.rec, g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, g.header, capacity,
-            g.exp_status, g.counters + CTR_EXPAND_TICKET, bw.hist, xy_keys);
+        const int run_blocks = (P + EXP_TILE - 1) / EXP_TILE;
+        if (chainfree_mode()) {
+            count_launch(2);
+            run_gather_kernel<<<run_blocks, SS_THREADS, 0, stream>>>(g.vis_ids[0], g.rec, g.vis_ids[1], g.vis_keys[0],
+                                                                    g.run_sums, g.header, capacity, bw.hist, xy_keys);
+            B200S_AFTER_LAUNCH(stream, debug);
+            scan_partials_kernel<<<1, SP_THREADS, 0, stream>>>(g.run_sums, g.run_prefix, run_blocks, g.header, 0);
+            B200S_AFTER_LAUNCH(stream, debug);
+            run_apply_kernel<<<run_blocks, SS_THREADS, 0, stream>>>(g.vis_keys[0], g.run_prefix, g.vis_keys[1],
+                                                                   bw.block_first, g.header, capacity);
+        } else {
+            sorted_scan_kernel<<<run_blocks, SS_THREADS, 0, stream>>>(
+                g.vis_ids[0], g.rec, g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, g.header, capacity,
+                g.exp_status, g.counters + CTR_EXPAND_TICKET, bw.hist, xy_keys);
+        }
         B200S_AFTER_LAUNCH(stream, debug);
         if (!fuse_expand) {
             expand_kernel<<<(unsigned)((n_hint + OUT_TILE - 1) / OUT_TILE), EXP_THREADS, 0, stream>>>(
@@ -1296,7 +1480,7 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
             if (p == 0 && fuse_expand && P > 0) {
                 expand_sort_count_kernel<<<(unsigned)sort_tiles, SORT_THREADS, SORT_XP_SMEM, stream>>>(
                     g.vis_ids[0], g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, bw.keys[1], bw.vals[1],
-                    g.header, capacity, bw.hist, bw.lookback, g.counters + CTR_SORT_TICKET0, lb_grouped_mode());
+                    g.header, capacity, bw.hist, bw.lookback, g.counters + CTR_SORT_TICKET0);
                 B200S_AFTER_LAUNCH(stream, debug);
                 cur ^= 1;
                 continue;
@@ -1306,8 +1490,7 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
             kern<<<(unsigned)sort_tiles, SORT_THREADS, smem, stream>>>(
                 bw.keys[cur], bw.vals[cur], bw.keys[cur ^ 1], bw.vals[cur ^ 1], g.header, &g.header->num_rendered,
                 capacity, p * SORT_RADIX_BITS, bw.hist + p * SORT_RADIX,
-                bw.lookback + (size_t)p * lb_rows(bw.sort_tiles) * SORT_RADIX, g.counters + CTR_SORT_TICKET0 + p,
-                lb_grouped_mode());
+                bw.lookback + (size_t)p * bw.sort_tiles * SORT_RADIX, g.counters + CTR_SORT_TICKET0 + p);
             B200S_AFTER_LAUNCH(stream, debug);
             cur ^= 1;
         }

@@ -52,6 +52,8 @@ __host__ __device__ inline size_t align_up(size_t x, size_t a = WS_ALIGN) {
 constexpr int SCAN_THREADS = B200S_SCAN_THREADS;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+constexpr int PRE_BLOCK = 256;        // Gaussians per preprocess_fwd block (= PRE_THREADS): granularity of pre_sums
+static_assert(SCAN_TILE % PRE_BLOCK == 0, "a scan tile covers whole preprocess blocks");
 
 // Radix sort geometry (see binning.cu).
 constexpr int SORT_RADIX_BITS = 8;
@@ -59,10 +61,6 @@ constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 16;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
-// Look-back rows of a sort pass: the tile rows in groups of LB_GROUP, each group followed by one group row
-// (binning.cu: lookback_exchange).
-constexpr int LB_GROUP = 16;
-inline int64_t lb_rows(int64_t tiles) { return tiles + (tiles + LB_GROUP - 1) / LB_GROUP; }
 constexpr int SORT_MAX_PASSES = 4;    // onesweep passes over the tile bits (<= 32 bits of tile id)
 constexpr int DEPTH_PASSES = 4;       // onesweep passes over the 32 depth bits
 
@@ -85,8 +83,13 @@ struct GeomWS {
     uint32_t* vis_ids[2];     // [P] their Gaussian ids; after the depth sort: front-to-back order
     unsigned long long* scan_status;   // [ceil(P / SCAN_TILE) + 1] decoupled look-back words
     uint32_t* depth_hist;     // [DEPTH_PASSES][SORT_RADIX]
-    uint32_t* depth_lookback; // [DEPTH_PASSES][lb_rows(ceil(P / SORT_TILE))][SORT_RADIX]
+    uint32_t* depth_lookback; // [DEPTH_PASSES][ceil(P / SORT_TILE)][SORT_RADIX]
     uint32_t* exp_status;     // [ceil(P / EXP_TILE) + 1] look-back words of the expansion
+    // chain-free scans (binning.cu): per-block sums written by the producing kernel, scanned by one block
+    unsigned long long* pre_sums;     // [ceil(P / PRE_BLOCK)] (sum of tiles_touched | visible count << 32) per preprocess block
+    unsigned long long* pre_prefix;   // [ceil(P / PRE_BLOCK)] exclusive prefix of pre_sums
+    unsigned long long* run_sums;     // [ceil(P / EXP_TILE)] instances per block of depth-sorted Gaussians
+    unsigned long long* run_prefix;   // [ceil(P / EXP_TILE)] exclusive prefix
     size_t zero_off, zero_bytes;   // scan_status..exp_status are contiguous: cleared every call
     int64_t depth_tiles;
     size_t bytes;
@@ -112,9 +115,13 @@ inline GeomWS carve_geom(void* base, int64_t P) {
     g.zero_off = off;
     g.scan_status = (unsigned long long*)take(8 * ((size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1));
     g.depth_hist = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * SORT_RADIX);
-    g.depth_lookback = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * lb_rows(g.depth_tiles) * SORT_RADIX);
+    g.depth_lookback = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * g.depth_tiles * SORT_RADIX);
     g.exp_status = (uint32_t*)take(4 * ((size_t)(P + EXP_TILE - 1) / EXP_TILE + 1));
     g.zero_bytes = off - g.zero_off;
+    g.pre_sums = (unsigned long long*)take(8 * ((size_t)(P + PRE_BLOCK - 1) / PRE_BLOCK));
+    g.pre_prefix = (unsigned long long*)take(8 * ((size_t)(P + PRE_BLOCK - 1) / PRE_BLOCK));
+    g.run_sums = (unsigned long long*)take(8 * ((size_t)(P + EXP_TILE - 1) / EXP_TILE));
+    g.run_prefix = (unsigned long long*)take(8 * ((size_t)(P + EXP_TILE - 1) / EXP_TILE));
     g.bytes = off;
     return g;
 }
@@ -150,7 +157,7 @@ struct BinWS {
     uint32_t* keys[2];     // [capacity] tile id of every instance (ping-pong)
     uint32_t* vals[2];     // [capacity] Gaussian id of every instance
     uint32_t* hist;        // [SORT_MAX_PASSES][SORT_RADIX] digit histograms -> exclusive bases
-    uint32_t* lookback;    // [SORT_MAX_PASSES][lb_rows(sort_tiles)][SORT_RADIX]
+    uint32_t* lookback;    // [SORT_MAX_PASSES][sort_tiles][SORT_RADIX]
     uint32_t* block_first; // [capacity / EXP_OUT_TILE + 2] first Gaussian of every expansion block
     size_t zero_bytes;     // hist+lookback are contiguous: bytes to clear before a sort
     int64_t sort_tiles;
@@ -170,7 +177,7 @@ inline BinWS carve_bin(void* base, int64_t capacity) {
     s.vals[1] = (uint32_t*)take(4 * (size_t)capacity);
     size_t z0 = off;
     s.hist = (uint32_t*)take(4 * (size_t)SORT_MAX_PASSES * SORT_RADIX);
-    s.lookback = (uint32_t*)take(4 * (size_t)SORT_MAX_PASSES * lb_rows(s.sort_tiles) * SORT_RADIX);
+    s.lookback = (uint32_t*)take(4 * (size_t)SORT_MAX_PASSES * s.sort_tiles * SORT_RADIX);
     s.zero_bytes = off - z0;
     s.block_first = (uint32_t*)take(4 * ((size_t)capacity / EXP_OUT_TILE + 2));
     s.bytes = off;
