@@ -207,7 +207,7 @@ int b200s_forward_preprocess(const B200sForwardArgs* a, b200s_stream_t stream_) 
     p.viewmatrix = a->viewmatrix; p.projmatrix = a->projmatrix; p.campos = a->campos;
     p.radii = a->radii; p.rec = g.rec; p.tiles_touched = g.tiles_touched; p.depth_bits = g.depth_bits;
     p.clamped = g.clamped;
-    p.header = g.header; p.counters = g.counters; p.block_sums = g.pre_sums;
+    p.header = g.header; p.counters = g.counters;
     {
         ProfScope ps(B200S_STAGE_PREPROCESS, stream);
         rc = launch_preprocess_fwd(p, stream);

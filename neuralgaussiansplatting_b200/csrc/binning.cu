@@ -268,118 +268,6 @@ scan_compact_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict_
     }
 }
 
-// ------------------------------------------------------------------- chain-free scans
-// The two prefix sums of the binning (tiles_touched in Gaussian-index order; instance counts in depth order) run
-// over 12-24 MB: at that size a chained look-back is LATENCY bound (scan_compact 35 us, sorted_scan 47 us at C3 for
-// ~5 us of HBM time, ncu r02i: issue slots 9 % busy). Chain-free form: the producing kernel leaves one partial sum per
-// block (preprocess_fwd: per 256 Gaussians; run_gather: per EXP_TILE depth-sorted Gaussians), ONE block scans the
-// partials, and the consumer applies the prefix of its first block — no tickets, no spinning, no status words.
-constexpr int SP_THREADS = 1024;
-__global__ void __launch_bounds__(SP_THREADS)
-scan_partials_kernel(const unsigned long long* __restrict__ sums, unsigned long long* __restrict__ prefix, int n,
-                     B200sHeader* header, int publish) {
-    __shared__ unsigned long long s_warp[SP_THREADS / 32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int per = (n + SP_THREADS - 1) / SP_THREADS;
-    const int i0 = min(n, tid * per), i1 = min(n, i0 + per);
-    unsigned long long mine = 0;
-    for (int i = i0; i < i1; ++i) mine += sums[i];
-    unsigned long long incl = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const unsigned long long t = __shfl_up_sync(FULL_MASK, incl, o);
-        if (lane >= o) incl += t;
-    }
-    if (lane == 31) s_warp[warp] = incl;
-    __syncthreads();
-    unsigned long long wex = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < SP_THREADS / 32; ++w) {
-        const unsigned long long t = s_warp[w];
-        if (w < warp) wex += t;
-        total += t;
-    }
-    unsigned long long run = wex + incl - mine;
-    for (int i = i0; i < i1; ++i) {
-        prefix[i] = run;
-        run += sums[i];
-    }
-    if (publish && tid == 0) {
-        header->num_rendered = (uint32_t)total;            // sum of tiles_touched (< 2^32, as in the chained scan)
-        header->num_visible = (uint32_t)(total >> 32);
-    }
-}
-
-// scan_compact_kernel without the chain: the exclusive prefix of a tile is pre_prefix of its first preprocess block.
-__global__ void __launch_bounds__(SCAN_THREADS)
-scan_apply_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict__ depth_bits,
-                  uint32_t* __restrict__ out, uint32_t* __restrict__ vis_keys, uint32_t* __restrict__ vis_ids,
-                  int P, const unsigned long long* __restrict__ pre_prefix) {
-    __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t tile = blockIdx.x;
-    const int64_t base = (int64_t)tile * SCAN_TILE + (int64_t)tid * SCAN_ITEMS;
-
-    uint32_t v[SCAN_ITEMS], dep[SCAN_ITEMS];
-    if (base + SCAN_ITEMS <= P) {
-        const uint4* src = reinterpret_cast<const uint4*>(in + base);
-        const uint4* dsrc = reinterpret_cast<const uint4*>(depth_bits + base);
-#pragma unroll
-        for (int i = 0; i < SCAN_ITEMS / 4; ++i) {
-            const uint4 t = src[i];
-            v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
-            const uint4 d = dsrc[i];
-            dep[4 * i] = d.x; dep[4 * i + 1] = d.y; dep[4 * i + 2] = d.z; dep[4 * i + 3] = d.w;
-        }
-    } else {
-#pragma unroll
-        for (int i = 0; i < SCAN_ITEMS; ++i) {
-            v[i] = (base + i < P) ? in[base + i] : 0u;
-            dep[i] = (base + i < P) ? depth_bits[base + i] : 0u;
-        }
-    }
-    uint32_t tsum = 0, vmask = 0;
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; ++i) {
-        if (v[i] != 0u) vmask |= 1u << i;
-        tsum += v[i]; v[i] = tsum;                     // thread-inclusive
-    }
-    const unsigned long long mine = (unsigned long long)tsum | ((unsigned long long)__popc(vmask) << 32);
-    unsigned long long incl = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const unsigned long long t = __shfl_up_sync(FULL_MASK, incl, o);
-        if (lane >= o) incl += t;
-    }
-    if (lane == 31) s_warp[warp] = incl;
-    __syncthreads();
-    unsigned long long warp_excl = 0;
-#pragma unroll
-    for (int w = 0; w < SCAN_THREADS / 32; ++w)
-        if (w < warp) warp_excl += s_warp[w];
-    const unsigned long long pre = pre_prefix[(size_t)tile * (SCAN_TILE / PRE_BLOCK)] + warp_excl + (incl - mine);
-    const uint32_t off = (uint32_t)pre;
-    uint32_t ci = (uint32_t)(pre >> 32);
-    if (base + SCAN_ITEMS <= P) {
-        uint4* dst = reinterpret_cast<uint4*>(out + base);
-#pragma unroll
-        for (int i = 0; i < SCAN_ITEMS / 4; ++i)
-            dst[i] = make_uint4(v[4 * i] + off, v[4 * i + 1] + off, v[4 * i + 2] + off, v[4 * i + 3] + off);
-    } else {
-#pragma unroll
-        for (int i = 0; i < SCAN_ITEMS; ++i)
-            if (base + i < P) out[base + i] = v[i] + off;
-    }
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; ++i) {
-        if ((vmask >> i) & 1u) {
-            vis_keys[ci] = dep[i];
-            vis_ids[ci] = (uint32_t)(base + i);
-            ++ci;
-        }
-    }
-}
-
 // ------------------------------------------------------------------------------- sort
 // Digit histograms of all passes in one read of the keys (used for the depth sort; the tile
 // sort's histogram is accumulated by the expansion kernel).
@@ -445,10 +333,7 @@ sort_scan_hist_kernel(uint32_t* hist, int from_diff) {
 #define B200S_RANK_COUNT_DEFAULT 0
 #endif
 #ifndef B200S_XY_KEYS_DEFAULT
-#define B200S_XY_KEYS_DEFAULT 0
-#endif
-#ifndef B200S_CHAINFREE_DEFAULT
-#define B200S_CHAINFREE_DEFAULT 0
+#define B200S_XY_KEYS_DEFAULT 1
 #endif
 #ifndef B200S_FUSE_EXPAND_DEFAULT
 #define B200S_FUSE_EXPAND_DEFAULT 0
@@ -906,108 +791,6 @@ sorted_scan_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __re
     }
 }
 
-// sorted_scan_kernel without the chain, in two kernels around scan_partials_kernel:
-// run_gather: the rectangle of every depth-sorted Gaussian as dense arrays + the instance count of every block
-// (+ the (x, y) digit histograms as range-adds); run_apply: block-local scan + the block's prefix -> run_end, block_first.
-__global__ void __launch_bounds__(SS_THREADS)
-run_gather_kernel(const uint32_t* __restrict__ sorted_ids, const SplatRec* __restrict__ rec,
-                  uint32_t* __restrict__ run_rmin, uint32_t* __restrict__ run_rwh,
-                  unsigned long long* __restrict__ run_sums, B200sHeader* header, int64_t capacity,
-                  uint32_t* __restrict__ hist, int xy_keys) {
-    __shared__ uint32_t s_warp[SS_THREADS / 32];
-    __shared__ uint32_t s_diff[2 * SORT_RADIX];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t n_vis = header->num_visible;
-    const bool overflow = (int64_t)header->num_rendered > capacity;
-    if (overflow && blockIdx.x == 0 && tid == 0) header->overflow = 1u;
-    if (xy_keys) for (int i = tid; i < 2 * SORT_RADIX; i += SS_THREADS) s_diff[i] = 0u;
-    __syncthreads();
-    const uint32_t g0 = blockIdx.x * EXP_TILE + tid * EXP_ITEMS;
-    uint32_t tsum = 0;
-    if (!overflow) {
-#pragma unroll
-        for (int k = 0; k < EXP_ITEMS; ++k) {
-            if (g0 + k < n_vis) {
-                const float4 q2 = rec[sorted_ids[g0 + k]].q2;
-                const uint32_t rmin = __float_as_uint(q2.z), rwh = __float_as_uint(q2.w);
-                const uint32_t w = rwh & 0xffffu, h = rwh >> 16;
-                run_rmin[g0 + k] = rmin;
-                run_rwh[g0 + k] = rwh;
-                tsum += w * h;
-                if (xy_keys && w * h != 0u) {
-                    const uint32_t x0 = rmin & 0xffffu, y0 = rmin >> 16;
-                    B200S_CHECK(x0 + w <= (uint32_t)SORT_RADIX && y0 + h <= (uint32_t)SORT_RADIX);
-                    atomicAdd(&s_diff[x0], h);
-                    if (x0 + w < (uint32_t)SORT_RADIX) atomicAdd(&s_diff[x0 + w], 0u - h);
-                    atomicAdd(&s_diff[SORT_RADIX + y0], w);
-                    if (y0 + h < (uint32_t)SORT_RADIX) atomicAdd(&s_diff[SORT_RADIX + y0 + h], 0u - w);
-                }
-            }
-        }
-    }
-    const uint32_t wsum = __reduce_add_sync(FULL_MASK, tsum);
-    if (lane == 0) s_warp[warp] = wsum;
-    __syncthreads();
-    if (tid == 0) {
-        unsigned long long tot = 0;
-#pragma unroll
-        for (int w = 0; w < SS_THREADS / 32; ++w) tot += s_warp[w];
-        run_sums[blockIdx.x] = tot;
-    }
-    if (xy_keys && !overflow) {
-        for (int i = tid; i < 2 * SORT_RADIX; i += SS_THREADS) {
-            const uint32_t c = s_diff[i];
-            if (c) atomicAdd(&hist[i], c);
-        }
-    }
-}
-
-__global__ void __launch_bounds__(SS_THREADS)
-run_apply_kernel(const uint32_t* __restrict__ run_rwh, const unsigned long long* __restrict__ run_prefix,
-                 uint32_t* __restrict__ run_end, uint32_t* __restrict__ block_first, const B200sHeader* header,
-                 int64_t capacity) {
-    __shared__ uint32_t s_warp[SS_THREADS / 32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t n_vis = header->num_visible;
-    if ((int64_t)header->num_rendered > capacity) return;
-    const uint32_t g0 = blockIdx.x * EXP_TILE + tid * EXP_ITEMS;
-    if (blockIdx.x * (uint32_t)EXP_TILE >= n_vis) return;
-    uint32_t cnt[EXP_ITEMS];
-    uint32_t tsum = 0;
-#pragma unroll
-    for (int k = 0; k < EXP_ITEMS; ++k) {
-        cnt[k] = 0;
-        if (g0 + k < n_vis) {
-            const uint32_t rwh = run_rwh[g0 + k];
-            cnt[k] = (rwh & 0xffffu) * (rwh >> 16);
-        }
-        tsum += cnt[k];
-    }
-    uint32_t incl = tsum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(FULL_MASK, incl, o);
-        if (lane >= o) incl += t;
-    }
-    if (lane == 31) s_warp[warp] = incl;
-    __syncthreads();
-    uint32_t wex = 0;
-#pragma unroll
-    for (int w = 0; w < SS_THREADS / 32; ++w)
-        if (w < warp) wex += s_warp[w];
-    uint32_t run = (uint32_t)run_prefix[blockIdx.x] + wex + incl - tsum;     // global start of this thread's first run
-#pragma unroll
-    for (int k = 0; k < EXP_ITEMS; ++k) {
-        if (g0 + k < n_vis) {
-            const uint32_t start = run, end = run + cnt[k];
-            run_end[g0 + k] = end;
-            for (uint32_t m = (start + OUT_TILE - 1) / OUT_TILE; (uint64_t)m * OUT_TILE < end; ++m)
-                block_first[m] = g0 + k;
-            run = end;
-        }
-    }
-}
-
 __global__ void __launch_bounds__(EXP_THREADS)
 expand_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* __restrict__ run_end,
               const uint32_t* __restrict__ run_rmin, const uint32_t* __restrict__ run_rwh,
@@ -1344,10 +1127,6 @@ static int set_sort_attr() {
 }
 using SortPassFn = void (*)(const uint32_t*, const uint32_t*, uint32_t*, uint32_t*, B200sHeader*, const uint32_t*, int64_t,
                             int, const uint32_t*, uint32_t*, uint32_t*);
-static int chainfree_mode() {
-    static int v = [] { const char* e = getenv("B200S_CHAINFREE"); return e && *e ? atoi(e) : B200S_CHAINFREE_DEFAULT; }();
-    return v;
-}
 static void sort_pass_kernel(int which, int pass, SortPassFn* fn, size_t* smem) {
     if (rank_by_count(which, pass)) { *fn = sort_onesweep_count_kernel; *smem = SORT_CR_SMEM; }
     else { *fn = rank_by_match(which, pass) ? sort_onesweep_kernel<true> : sort_onesweep_kernel<false>; *smem = SORT_SMEM; }
@@ -1361,19 +1140,10 @@ int launch_scan_and_depth_sort(int P, const GeomWS& g, bool debug, cudaStream_t 
     {
         ProfScope ps(B200S_STAGE_SCAN, stream);
         const int tiles = (P + SCAN_TILE - 1) / SCAN_TILE;
-        if (chainfree_mode()) {
-            count_launch(2);
-            scan_partials_kernel<<<1, SP_THREADS, 0, stream>>>(g.pre_sums, g.pre_prefix, (P + PRE_BLOCK - 1) / PRE_BLOCK,
-                                                              g.header, 1);
-            B200S_AFTER_LAUNCH(stream, debug);
-            scan_apply_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(g.tiles_touched, g.depth_bits, g.point_offsets,
-                                                                 g.vis_keys[0], g.vis_ids[0], P, g.pre_prefix);
-        } else {
-            count_launch();
-            scan_compact_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(g.tiles_touched, g.depth_bits, g.point_offsets,
-                                                                   g.vis_keys[0], g.vis_ids[0], P, g.scan_status,
-                                                                   g.counters, g.header);
-        }
+        count_launch();
+        scan_compact_kernel<<<tiles, SCAN_THREADS, 0, stream>>>(g.tiles_touched, g.depth_bits, g.point_offsets,
+                                                               g.vis_keys[0], g.vis_ids[0], P, g.scan_status,
+                                                               g.counters, g.header);
         B200S_AFTER_LAUNCH(stream, debug);
     }
     {
@@ -1445,21 +1215,9 @@ int launch_binning(int P, const GeomWS& g, const BinWS& bw, int64_t capacity, in
         // the depth sort's spare buffers (and its no longer needed sorted keys) hold the runs
         ProfScope ps(B200S_STAGE_EXPAND, stream);
         count_launch(2);
-        const int run_blocks = (P + EXP_TILE - 1) / EXP_TILE;
-        if (chainfree_mode()) {
-            count_launch(2);
-            run_gather_kernel<<<run_blocks, SS_THREADS, 0, stream>>>(g.vis_ids[0], g.rec, g.vis_ids[1], g.vis_keys[0],
-                                                                    g.run_sums, g.header, capacity, bw.hist, xy_keys);
-            B200S_AFTER_LAUNCH(stream, debug);
-            scan_partials_kernel<<<1, SP_THREADS, 0, stream>>>(g.run_sums, g.run_prefix, run_blocks, g.header, 0);
-            B200S_AFTER_LAUNCH(stream, debug);
-            run_apply_kernel<<<run_blocks, SS_THREADS, 0, stream>>>(g.vis_keys[0], g.run_prefix, g.vis_keys[1],
-                                                                   bw.block_first, g.header, capacity);
-        } else {
-            sorted_scan_kernel<<<run_blocks, SS_THREADS, 0, stream>>>(
-                g.vis_ids[0], g.rec, g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, g.header, capacity,
-                g.exp_status, g.counters + CTR_EXPAND_TICKET, bw.hist, xy_keys);
-        }
+        sorted_scan_kernel<<<(P + EXP_TILE - 1) / EXP_TILE, SS_THREADS, 0, stream>>>(
+            g.vis_ids[0], g.rec, g.vis_keys[1], g.vis_ids[1], g.vis_keys[0], bw.block_first, g.header, capacity,
+            g.exp_status, g.counters + CTR_EXPAND_TICKET, bw.hist, xy_keys);
         B200S_AFTER_LAUNCH(stream, debug);
         if (!fuse_expand) {
             expand_kernel<<<(unsigned)((n_hint + OUT_TILE - 1) / OUT_TILE), EXP_THREADS, 0, stream>>>(

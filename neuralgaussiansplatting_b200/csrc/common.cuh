@@ -52,8 +52,6 @@ __host__ __device__ inline size_t align_up(size_t x, size_t a = WS_ALIGN) {
 constexpr int SCAN_THREADS = B200S_SCAN_THREADS;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
-constexpr int PRE_BLOCK = 256;        // Gaussians per preprocess_fwd block (= PRE_THREADS): granularity of pre_sums
-static_assert(SCAN_TILE % PRE_BLOCK == 0, "a scan tile covers whole preprocess blocks");
 
 // Radix sort geometry (see binning.cu).
 constexpr int SORT_RADIX_BITS = 8;
@@ -85,11 +83,6 @@ struct GeomWS {
     uint32_t* depth_hist;     // [DEPTH_PASSES][SORT_RADIX]
     uint32_t* depth_lookback; // [DEPTH_PASSES][ceil(P / SORT_TILE)][SORT_RADIX]
     uint32_t* exp_status;     // [ceil(P / EXP_TILE) + 1] look-back words of the expansion
-    // chain-free scans (binning.cu): per-block sums written by the producing kernel, scanned by one block
-    unsigned long long* pre_sums;     // [ceil(P / PRE_BLOCK)] (sum of tiles_touched | visible count << 32) per preprocess block
-    unsigned long long* pre_prefix;   // [ceil(P / PRE_BLOCK)] exclusive prefix of pre_sums
-    unsigned long long* run_sums;     // [ceil(P / EXP_TILE)] instances per block of depth-sorted Gaussians
-    unsigned long long* run_prefix;   // [ceil(P / EXP_TILE)] exclusive prefix
     size_t zero_off, zero_bytes;   // scan_status..exp_status are contiguous: cleared every call
     int64_t depth_tiles;
     size_t bytes;
@@ -118,10 +111,6 @@ inline GeomWS carve_geom(void* base, int64_t P) {
     g.depth_lookback = (uint32_t*)take(4 * (size_t)DEPTH_PASSES * g.depth_tiles * SORT_RADIX);
     g.exp_status = (uint32_t*)take(4 * ((size_t)(P + EXP_TILE - 1) / EXP_TILE + 1));
     g.zero_bytes = off - g.zero_off;
-    g.pre_sums = (unsigned long long*)take(8 * ((size_t)(P + PRE_BLOCK - 1) / PRE_BLOCK));
-    g.pre_prefix = (unsigned long long*)take(8 * ((size_t)(P + PRE_BLOCK - 1) / PRE_BLOCK));
-    g.run_sums = (unsigned long long*)take(8 * ((size_t)(P + EXP_TILE - 1) / EXP_TILE));
-    g.run_prefix = (unsigned long long*)take(8 * ((size_t)(P + EXP_TILE - 1) / EXP_TILE));
     g.bytes = off;
     return g;
 }

@@ -26,7 +26,6 @@ struct PreprocessParams {
     uint8_t* clamped;
     B200sHeader* header;
     uint32_t* counters;
-    unsigned long long* block_sums;   // [blocks] sum of tiles_touched | visible count << 32 of every block
 };
 
 struct BlendFwdParams {

@@ -15,7 +15,7 @@
 namespace b200s {
 
 
-constexpr int PRE_THREADS = PRE_BLOCK;
+constexpr int PRE_THREADS = 256;
 constexpr int SH_ROW_FLOATS = 48;   // 16 coefficients x RGB
 constexpr int SH_ROW_PAD = 52;      // 208 B rows: 13 x 16 B => LDS.128 conflict-free
 constexpr size_t PRE_SMEM_SH16 = (size_t)PRE_THREADS * SH_ROW_PAD * sizeof(float);
@@ -215,22 +215,6 @@ preprocess_fwd_kernel(const __grid_constant__ PreprocessParams p) {
             p.rec[idx] = r;
             p.depth_bits[idx] = __float_as_uint(depth);
             p.clamped[idx] = (uint8_t)clamp_bits;
-        }
-    }
-    // per-block (sum of tiles_touched, number of visible Gaussians): lets the scan behind this kernel run without a
-    // look-back chain (binning.cu: scan_partials_kernel / scan_apply_kernel)
-    {
-        __shared__ unsigned long long s_part[PRE_THREADS / 32];
-        const uint32_t t = in_range ? (uint32_t)tiles : 0u;
-        const uint32_t wsum = __reduce_add_sync(FULL_MASK, t);
-        const uint32_t wvis = __popc(__ballot_sync(FULL_MASK, t != 0u));
-        if ((tid & 31) == 0) s_part[tid >> 5] = (unsigned long long)wsum | ((unsigned long long)wvis << 32);
-        __syncthreads();
-        if (tid == 0) {
-            unsigned long long tot = 0;
-#pragma unroll
-            for (int w = 0; w < PRE_THREADS / 32; ++w) tot += s_part[w];
-            p.block_sums[blockIdx.x] = tot;
         }
     }
 }
