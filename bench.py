@@ -240,7 +240,8 @@ def run_ours(args, rank, local_rank, world, dev):
                                                          multimem=(True if args.multimem else False if args.exact_collective else None),
                                                          factored=not args.dense_collective,
                                                          gather_push=not args.gather_pull,
-                                                         priority=0 if args.compute_priority else -1)
+                                                         priority=0 if args.compute_priority else -1,
+                                                         fast_reconstruct=not args.exact_reconstruct)
             except Exception as e:  # noqa: BLE001 — no peer mappings on this box (no NVLink P2P / IPC): say so, use NCCL
                 print(f"[bench] rank {rank}: peer-memory collective unavailable ({e}); falling back to NCCL",
                       file=sys.stderr)
@@ -251,7 +252,9 @@ def run_ours(args, rank, local_rank, world, dev):
                                f"{reducer.ctas} CTAs, {reducer.mem.backend} mappings"
                                + (", factored SH gradient: 11 dense floats summed + 3 dL/dRGB floats gathered per Gaussian "
                                   "and view (" + ("multimem.st push" if reducer.gather_push else "peer-load pull")
-                                  + "), dL/dsh rebuilt by b200s_sh_grad_reconstruct (bit-identical to the dense sum)"
+                                  + "), dL/dsh rebuilt by b200s_sh_grad_reconstruct ("
+                                  + ("fused-multiply-add form, identical on every rank, ~1e-7 of the dense sum"
+                                     if (reducer.multimem and reducer.fast_reconstruct) else "bit-identical to the dense sum") + ")"
                                   if reducer.factored else "")
                                + (", rasterizer on a high-priority stream" if args.compute_priority else "")
                                + ("" if not args.sparse_collective or reducer.multimem or reducer.factored else
@@ -1000,6 +1003,8 @@ def main():
                     help="peer collective: use the view's radii to skip all-zero dL/dSH rows (exact; fewer NVLink "
                          "bytes but fewer loads in flight per CTA — slower at 2 GPUs, see DESIGN.md §7)")
     ap.add_argument("--multimem", action="store_true", help="peer collective: NVSwitch multimem.ld_reduce/st")
+    ap.add_argument("--exact-reconstruct", action="store_true",
+                    help="rebuild dL/dsh with the bit-exact kernel even when the dense part is summed in the switch")
     ap.add_argument("--exact-collective", action="store_true",
                     help="peer collective: always the rank-order two-shot sum over peer loads (bit-identical to a "
                          "fixed-order sum); default: in-switch multimem sum of the dense part with 4+ ranks")

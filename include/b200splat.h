@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define B200S_ABI_VERSION 2
+#define B200S_ABI_VERSION 3
 
 /* tile size is fixed by the reference (cuda_rasterizer/config.h:16-17) */
 #define B200S_BLOCK_X 16
@@ -332,6 +332,11 @@ typedef struct B200sShGradArgs {
     const float* factors;        /* [views][stride_floats] */
     uint64_t stride_floats;      /* >= 3*P + 4 */
     float* dL_dsh;               /* [P,M,3], 16-byte aligned */
+    int32_t fast;                /* 0: the exact form above (separate product and sum roundings, IEEE sqrt / divide).
+                                  * 1: fused multiply-adds and an rsqrt-based direction: about half the instructions;
+                                  *    the same sum to ~1e-7 relative, identical on every rank that holds the same
+                                  *    factors (for collectives whose dense part is not a rank-order sum anyway). */
+    int32_t reserved_;
 } B200sShGradArgs;
 int b200s_sh_grad_reconstruct(const B200sShGradArgs* args, b200s_stream_t stream);
 

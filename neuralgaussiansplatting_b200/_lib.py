@@ -79,7 +79,7 @@ class IdxmapArgs(C.Structure):
 
 
 MAX_PEERS = 16
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class PeerReduceArgs(C.Structure):
@@ -97,6 +97,7 @@ class ShGradArgs(C.Structure):
     _fields_ = [
         ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("views", C.c_int32),
         ("means3D", C.c_void_p), ("factors", C.c_void_p), ("stride_floats", C.c_uint64), ("dL_dsh", C.c_void_p),
+        ("fast", C.c_int32), ("reserved_", C.c_int32),
     ]
 
 

@@ -444,6 +444,7 @@ extern "C" int b200s_sh_grad_reconstruct(const B200sShGradArgs* a, b200s_stream_
     if (a->M < (a->D + 1) * (a->D + 1) || a->M > 16) return B200S_E_BADARG;
     if (a->stride_floats < 3ull * (uint64_t)a->P + 4ull) return B200S_E_BADARG;
     if ((uintptr_t)a->dL_dsh & 15u) return B200S_E_BADARG;
+    if (a->fast != 0 && a->fast != 1) return B200S_E_BADARG;
     return launch_sh_grad_reconstruct(*a, (cudaStream_t)stream_);
 }
 

@@ -318,9 +318,10 @@ class PeerGradientAllReduce:
 
     def __init__(self, P: int, sh_coeffs: int = 16, device=None, group=None, n_buffers: int = 2, ctas: int = 0,
                  multimem: Optional[bool] = None, backend: str = "auto", factored: bool = True,
-                 gather_push: bool = True, priority: int = 0):
+                 gather_push: bool = True, priority: int = 0, fast_reconstruct: bool = True):
         from . import _lib
         self._libmod = _lib
+        self.fast_reconstruct = bool(fast_reconstruct)
         self._lib = _lib.load()
         self.group = group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
@@ -465,6 +466,9 @@ class PeerGradientAllReduce:
             sg.factors = self._flat[self._cur].data_ptr() + 4 * self.n_floats
             sg.stride_floats = self.slot_floats
             sg.dL_dsh = views["shs"].data_ptr()
+            # in-switch dense sum: the step is not a rank-order sum anyway, so the rebuild may use the fused form
+            # (half the instructions; identical on every rank); the exact collectives keep the bit-exact rebuild
+            sg.fast = 1 if (self.multimem and self.fast_reconstruct) else 0
             self._means_keep = means3D
             self._libmod.check(self._lib.b200s_sh_grad_reconstruct(C.byref(sg), self._stream.cuda_stream),
                                "b200s_sh_grad_reconstruct")

@@ -71,6 +71,14 @@ def test_reconstruct_equals_fixed_order_sum_of_dense_rows(dev, cfg_name, degree,
     assert torch.isfinite(got).all()
     assert float(expect.abs().max()) > 0
     assert torch.equal(got, expect), float((got - expect).abs().max())
+    # fast form (fused multiply-adds, rsqrt direction; what the in-switch collective uses): same sum to rounding
+    fastv = torch.full_like(expect, float("nan"))
+    a.fast, a.dL_dsh = 1, fastv.data_ptr()
+    _lib.check(lib.b200s_sh_grad_reconstruct(C.byref(a), torch.cuda.current_stream().cuda_stream), "reconstruct fast")
+    torch.cuda.synchronize()
+    assert torch.isfinite(fastv).all()
+    assert float((fastv - expect).abs().max()) <= 2e-6 * float(expect.abs().max()), float((fastv - expect).abs().max())
+    assert torch.equal(fastv == 0, expect == 0)          # culled rows stay exactly zero
     # the factor block carries the view's camera centre behind the 3P factors
     for i, v in enumerate(views):
         cam = make_camera(cfg, v, device=dev)

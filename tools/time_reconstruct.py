@@ -28,14 +28,16 @@ for views in (1, 2, 4, 8):
     a.P, a.D, a.M, a.views = P, 3, 16, views
     a.means3D, a.factors, a.stride_floats, a.dL_dsh = means.data_ptr(), f.data_ptr(), slot, out.data_ptr()
     st = torch.cuda.current_stream().cuda_stream
-    for _ in range(3):
-        lib.b200s_sh_grad_reconstruct(C.byref(a), st)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(20):
-        lib.b200s_sh_grad_reconstruct(C.byref(a), st)
-    e1.record(); torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / 20
-    nbytes = P * (12 * views + 12 + 192)
-    res[f"views{views}"] = {"ms": round(ms, 4), "GBps": round(nbytes / ms / 1e6, 1)}
+    for fast in (0, 1):
+        a.fast = fast
+        for _ in range(3):
+            lib.b200s_sh_grad_reconstruct(C.byref(a), st)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            lib.b200s_sh_grad_reconstruct(C.byref(a), st)
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 20
+        nbytes = P * (12 * views + 12 + 192)
+        res[f"views{views}_{'fast' if fast else 'exact'}"] = {"ms": round(ms, 4), "GBps": round(nbytes / ms / 1e6, 1)}
 print(json.dumps(res))
