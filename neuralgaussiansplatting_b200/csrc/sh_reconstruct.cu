@@ -35,7 +35,7 @@ struct ShReconParams {
 };
 
 #ifndef B200S_SR_MINB
-#define B200S_SR_MINB 4
+#define B200S_SR_MINB 5
 #endif
 template <bool SH16, bool FAST, int DEG>     // DEG < 0: degree read from the parameters
 __global__ void __launch_bounds__(SR_THREADS, B200S_SR_MINB)
