@@ -196,9 +196,29 @@ def load() -> C.CDLL:
         return _lib
     path = lib_path()
     if not path.exists() or os.environ.get("B200S_REBUILD"):
-        _build.build(force=bool(os.environ.get("B200S_REBUILD")))
+        # several ranks of a torchrun job may arrive here together: one builds, the others wait for the lock and
+        # then find the library in place
+        import fcntl
+        _build.PKG_DIR.joinpath("_obj").mkdir(exist_ok=True)
+        with open(_build.PKG_DIR / "_obj" / ".build.lock", "w") as lock:
+            fcntl.flock(lock, fcntl.LOCK_EX)
+            try:
+                if not path.exists() or os.environ.get("B200S_REBUILD"):
+                    _build.build(force=bool(os.environ.get("B200S_REBUILD")))
+            finally:
+                fcntl.flock(lock, fcntl.LOCK_UN)
     if not path.exists():
         raise RuntimeError(f"{path} is missing and could not be built; b200splat has no fallback path")
+    if path == _build.LIB_PATH:
+        # an existing library is used as it is (the GPU box receives it prebuilt); say so when the sources are newer
+        try:
+            newest = max(p.stat().st_mtime for p in [*(_build.CSRC / s for s in _build.SOURCES), *_build.HEADERS])
+            if newest > path.stat().st_mtime + 1.0:
+                import sys
+                print(f"[b200splat] {path.name} is older than csrc/: rebuild with "
+                      f"`python -m neuralgaussiansplatting_b200.build` or B200S_REBUILD=1", file=sys.stderr)
+        except OSError:
+            pass
     lib = C.CDLL(str(path))
     for name, restype, argtypes in SYMBOLS:
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported

@@ -58,11 +58,29 @@ def l1_ssim_loss(image: torch.Tensor, gt: torch.Tensor, lambda_dssim: float = 0.
     return _L1SSIM.apply(image, gt, float(lambda_dssim))
 
 
+class _Component(torch.autograd.Function):
+    """One term of the photometric loss as a differentiable scalar: which = 1 -> L1, which = 2 -> SSIM. The fused
+    kernels emit d((1-lambda) L1 + lambda (1-SSIM))/dimage; lambda = 0 gives dL1/dimage, lambda = 1 gives -dSSIM/dimage."""
+
+    @staticmethod
+    def forward(ctx, image, gt, which):
+        out, grad = fused_l1_ssim(image, gt, 0.0 if which == 1 else 1.0, want_grad=image.requires_grad)
+        ctx.save_for_backward(grad)
+        ctx.sign = 1.0 if which == 1 else -1.0
+        return out[which]
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return grad * (g * ctx.sign), None, None
+
+
 def l1_loss(network_output: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
-    """utils/loss_utils.py:17-18 (value only)."""
-    return fused_l1_ssim(network_output, gt, 0.0, want_grad=False)[0][1]
+    """utils/loss_utils.py:17-18, differentiable w.r.t. the first argument like the reference's (the second is a
+    constant, as in train.py:91). For the training step prefer l1_ssim_loss: one fused call for both terms."""
+    return _Component.apply(network_output, gt, 1)
 
 
 def ssim(img1: torch.Tensor, img2: torch.Tensor) -> torch.Tensor:
-    """utils/loss_utils.py:34-43 with the defaults window_size=11, size_average=True (value only)."""
-    return fused_l1_ssim(img1, img2, 0.0, want_grad=False)[0][2]
+    """utils/loss_utils.py:34-43 with the defaults window_size=11, size_average=True; differentiable w.r.t. img1."""
+    return _Component.apply(img1, img2, 2)

@@ -123,3 +123,22 @@ def test_fused_loss_autograd_and_reproducibility():
     b = L.fused_l1_ssim(x.detach(), gt.to(dev))[0]
     assert torch.equal(a, b)                                                     # fixed-order reduction
     assert abs(float(L.ssim(gt.to(dev), gt.to(dev))) - 1.0) < 1e-6 and float(L.l1_loss(gt.to(dev), gt.to(dev))) == 0.0
+
+
+def Hh_rel_l2(a, b):
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+@pytest.mark.gpu
+def test_reference_style_composition_is_differentiable(dev):
+    """train.py:91-92 writes the loss as (1 - l) * l1_loss(image, gt) + l * (1 - ssim(image, gt)) and calls
+    .backward(): the drop-in l1_loss / ssim must carry gradients, and agree with the fused call."""
+    g = torch.Generator().manual_seed(5)
+    img = torch.rand(3, 57, 83, generator=g).to(dev).requires_grad_(True)
+    gt = torch.rand(3, 57, 83, generator=g).to(dev)
+    lam = 0.2
+    loss = (1.0 - lam) * L.l1_loss(img, gt) + lam * (1.0 - L.ssim(img, gt))
+    loss.backward()
+    out, grad = L.fused_l1_ssim(img.detach(), gt, lam)
+    assert abs(float(loss) - float(out[0])) < 2e-6
+    assert img.grad is not None and Hh_rel_l2(img.grad, grad) < 1e-5

@@ -138,6 +138,18 @@ def test_ragged_image_sizes_forward_and_backward(ref, dev, wh):
 
 
 @needs_ref
+@pytest.mark.parametrize("wh", [(4112, 48), (48, 4112)])
+def test_grids_wider_than_256_tiles_use_tile_id_keys(ref, dev, wh):
+    """More than 256 tile columns (or rows): the (x, y) sort keys do not fit 8 + 8 bits, so the binning falls back to
+    tile-id keys on the default path (csrc/binning.cu: launch_binning). Forward state bit-exact, gradients as usual."""
+    import dataclasses
+    from neuralgaussiansplatting_b200.synthetic import CONFIGS
+    cfg = dataclasses.replace(CONFIGS["T0"], width=wh[0], height=wh[1])
+    res = check_against_reference(ref, cfg, dev)
+    assert res["num_rendered"][0] > 0
+
+
+@needs_ref
 def test_huge_gaussians_cover_every_tile(ref, dev):
     """A few Gaussians whose rectangle is the whole tile grid (the load-balanced expansion path)."""
     cfg, sc, cam = Hh.scene_on("T0", dev, P=64)
