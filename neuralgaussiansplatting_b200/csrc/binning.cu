@@ -129,19 +129,29 @@ __device__ __forceinline__ T warp_lookback(const T* status, int64_t tile, B200sH
 #define B200S_LB_DEPTH 8
 #endif
 constexpr int LB_DEPTH = B200S_LB_DEPTH;
+// The depth sort runs over the visible Gaussians only (314 tiles at C3): ALL of its tiles are resident at once, every
+// count is published within the same few microseconds, and tile t simply has to add up t predecessor words — its
+// pass ends when the LAST tile has walked them all, a chain of t / depth dependent round trips. Those passes take a
+// deeper window (B200S_LB_DEPTH_DS); the tile passes (1,900+ tiles, ~450 resident) keep 8, where deeper windows were
+// measured slower (reads past the first inclusive word, register pressure).
+#ifndef B200S_LB_DEPTH_DS
+#define B200S_LB_DEPTH_DS 8
+#endif
+constexpr int LB_DEPTH_DS = B200S_LB_DEPTH_DS;
+template <int DEPTH>
 __device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t stride, int64_t tile, B200sHeader* header) {
     uint32_t excl = 0;
     int64_t t = tile - 1;
     int spins = 0;
     while (t >= 0) {
-        uint32_t w[LB_DEPTH];
+        uint32_t w[DEPTH];
 #pragma unroll
-        for (int i = 0; i < LB_DEPTH; ++i)
+        for (int i = 0; i < DEPTH; ++i)
             w[i] = (t - i >= 0) ? ld_volatile_u32(col + (size_t)(t - i) * stride) : FLAG_INCL;
         bool done = false, stop = false;
         int take = 0;
 #pragma unroll
-        for (int i = 0; i < LB_DEPTH; ++i) {
+        for (int i = 0; i < DEPTH; ++i) {
             if (!done && !stop) {
                 const uint32_t f = w[i] & 3u;
                 if (f == 0u) stop = true;
@@ -160,13 +170,14 @@ __device__ __forceinline__ uint32_t thread_lookback(const uint32_t* col, size_t 
 
 // Publishes this tile's digit count (unless the caller already has), finds its exclusive prefix and publishes the
 // inclusive one; `col` = the pass's look-back array + this thread's digit. Returns the exclusive prefix.
+template <int DEPTH>
 __device__ __forceinline__ uint32_t lookback_exchange(uint32_t* col, size_t stride, int64_t tile, uint32_t count,
                                                       bool already_published, B200sHeader* header) {
     uint32_t* mine = col + (size_t)tile * stride;
     if (!already_published) st_volatile_u32(mine, (count << 2) | (tile == 0 ? FLAG_INCL : FLAG_AGG));
     uint32_t excl = 0;
     if (tile != 0) {
-        excl = thread_lookback(col, stride, tile, header);
+        excl = thread_lookback<DEPTH>(col, stride, tile, header);
         st_volatile_u32(mine, ((excl + count) << 2) | FLAG_INCL);
     }
     return excl;
@@ -347,7 +358,7 @@ constexpr size_t SORT_SMEM = (size_t)SORT_TILE * 4 + (size_t)SORT_TILE * 4 +
 // One stable 8-bit pass over (u32 key, u32 value) pairs: chained look-back over SORT_TILE-key
 // blocks ("onesweep"), in-block ranking by warp match. `n` is read from device memory; a count
 // above `capacity` (binning overflow) makes the pass a no-op.
-template <bool USE_MATCH>
+template <bool USE_MATCH, int LBD>
 __global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
 sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
@@ -456,7 +467,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         s_keys[pos] = key[k];
         s_vals[pos] = val[k];
     }
-    const uint32_t excl = lookback_exchange(lookback + tid, SORT_RADIX, (int64_t)tile, count, true, header);
+    const uint32_t excl = lookback_exchange<LBD>(lookback + tid, SORT_RADIX, (int64_t)tile, count, true, header);
     s_gbase[tid] = bin_base[tid] + excl - dstart;
     __syncthreads();
     for (uint32_t i = tid; i < tile_n; i += SORT_THREADS) {
@@ -625,7 +636,7 @@ __device__ __forceinline__ void cr_scatter_tile(const CrSmem& sm, uint32_t tile,
     __syncthreads();
     const uint32_t dstart = sm.dstart[tid];
     const uint32_t count = sm.dstart[tid + 1] - dstart;
-    const uint32_t excl = lookback_exchange(lookback + tid, SORT_RADIX, (int64_t)tile, count, false, header);
+    const uint32_t excl = lookback_exchange<LB_DEPTH>(lookback + tid, SORT_RADIX, (int64_t)tile, count, false, header);
     sm.gbase[tid] = bin_base[tid] + excl - dstart;
     __syncthreads();
     for (uint32_t i = tid; i < tile_n; i += SORT_THREADS) {
@@ -1119,8 +1130,12 @@ static bool rank_by_count(int which, int pass) {
     return (mask >> (which * 4 + pass)) & 1;
 }
 static int set_sort_attr() {
-    B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
-    B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+    B200S_SET_FUNC_ATTR_ONCE((sort_onesweep_kernel<true, LB_DEPTH>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+    B200S_SET_FUNC_ATTR_ONCE((sort_onesweep_kernel<false, LB_DEPTH>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+    if (LB_DEPTH_DS != LB_DEPTH) {
+        B200S_SET_FUNC_ATTR_ONCE((sort_onesweep_kernel<true, LB_DEPTH_DS>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+        B200S_SET_FUNC_ATTR_ONCE((sort_onesweep_kernel<false, LB_DEPTH_DS>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+    }
     B200S_SET_FUNC_ATTR_ONCE(sort_onesweep_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_CR_SMEM);
     B200S_SET_FUNC_ATTR_ONCE(expand_sort_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_XP_SMEM);
     return 0;
@@ -1129,7 +1144,13 @@ using SortPassFn = void (*)(const uint32_t*, const uint32_t*, uint32_t*, uint32_
                             int, const uint32_t*, uint32_t*, uint32_t*);
 static void sort_pass_kernel(int which, int pass, SortPassFn* fn, size_t* smem) {
     if (rank_by_count(which, pass)) { *fn = sort_onesweep_count_kernel; *smem = SORT_CR_SMEM; }
-    else { *fn = rank_by_match(which, pass) ? sort_onesweep_kernel<true> : sort_onesweep_kernel<false>; *smem = SORT_SMEM; }
+    else if (which == 0) {
+        *fn = rank_by_match(which, pass) ? sort_onesweep_kernel<true, LB_DEPTH_DS> : sort_onesweep_kernel<false, LB_DEPTH_DS>;
+        *smem = SORT_SMEM;
+    } else {
+        *fn = rank_by_match(which, pass) ? sort_onesweep_kernel<true, LB_DEPTH> : sort_onesweep_kernel<false, LB_DEPTH>;
+        *smem = SORT_SMEM;
+    }
 }
 
 // Stage 1b: point_offsets + num_rendered, compaction of the visible Gaussians, depth sort.
