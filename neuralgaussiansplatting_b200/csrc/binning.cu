@@ -129,11 +129,9 @@ __device__ __forceinline__ T warp_lookback(const T* status, int64_t tile, B200sH
 #define B200S_LB_DEPTH 8
 #endif
 constexpr int LB_DEPTH = B200S_LB_DEPTH;
-// The depth sort runs over the visible Gaussians only (314 tiles at C3): ALL of its tiles are resident at once, every
-// count is published within the same few microseconds, and tile t simply has to add up t predecessor words — its
-// pass ends when the LAST tile has walked them all, a chain of t / depth dependent round trips. Those passes take a
-// deeper window (B200S_LB_DEPTH_DS); the tile passes (1,900+ tiles, ~450 resident) keep 8, where deeper windows were
-// measured slower (reads past the first inclusive word, register pressure).
+// The window depth is a template parameter, separately selectable for the depth-sort passes (B200S_LB_DEPTH_DS): all of
+// their tiles (314 at C3) are resident at once, so a deeper window looked attractive there. Measured: it is not — C3
+// sort 0.263 (8) / 0.270 (16) / 0.280 ms (32), C4 0.484 / 0.493 / 0.505 (profiles/r02r_lb_depth_ds.log). Both stay at 8.
 #ifndef B200S_LB_DEPTH_DS
 #define B200S_LB_DEPTH_DS 8
 #endif
