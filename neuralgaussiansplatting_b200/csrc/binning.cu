@@ -20,8 +20,13 @@
 //                   rasterizer_impl.cu:98-109). The prefix sum of tiles_touched in sorted order is
 //                   fused in as a chained look-back between blocks, and so is the digit histogram
 //                   of the tile ids.
-//  * tile sort      a STABLE onesweep over the tile bits only (2 passes for up to 65,536 tiles):
-//                   the instances of a tile keep their emission (= depth) order.
+//  * tile sort      a STABLE onesweep over the tile position only (2 passes for up to 65,536 tiles):
+//                   the instances of a tile keep their emission (= depth) order. The key is row << 8 | column
+//                   (grids up to 256 x 256 tiles; the tile id beyond): same order as the tile id, but both
+//                   digits are tile coordinates, so their histograms are range-adds per Gaussian (sorted_scan)
+//                   instead of shared-memory atomics per instance (expand), and a pass sees fewer distinct
+//                   digits. Opt-in alternatives, bit-identical (tests/test_binning_modes_gpu.py): counting-rank
+//                   passes without MATCH / VOTE, and the expansion fused into the first tile pass.
 //  * ranges         as the reference.
 //  Traffic: ~16 B x 2 passes per instance + 16 B x 4 passes per visible Gaussian, instead of
 //  ~152 B per instance. The 64-bit keys are never materialised (the parity export rebuilds them).
