@@ -214,6 +214,28 @@ int b200s_idxmap_backward(int32_t P, int32_t W, int32_t H, const int32_t* out_id
                           const float* grad_feature, float* dL_dfeature_vector,
                           b200s_stream_t stream);
 
+/* ---- idxmap forward without a caller workspace. No counterpart in the reference (its binding
+ *      allocates through torch on every call); added for hosts of this library that cannot
+ *      hand over a workspace: a render loop embedded in an application whose device memory is
+ *      already owned in full by another allocator (a pre-sized arena, a framework pool capped
+ *      at a memory fraction), or a loop that must not run into cudaMalloc's device-wide
+ *      synchronisation. Same inputs, outputs, results and status codes as the workspace variant
+ *      above; args->ws and args->ws_bytes are ignored. The 8-byte-per-pixel z-buffer is a fixed
+ *      array inside the library image instead, so:
+ *        - W*H may be at most B200S_IDXMAP_STATIC_MAX_PIXELS (2^21, enough for 1920x1080);
+ *          a larger view returns B200S_E_WORKSPACE before anything is enqueued;
+ *        - every GPU that loads the library holds those 16 MiB until the process exits;
+ *        - the array is one per GPU and shared by all calls: it is re-initialised at the start
+ *          of each call, and two calls that overlap on one GPU (two streams, two threads)
+ *          corrupt each other. Serialise them;
+ *        - the device the stream belongs to must be the current device. The first call on each
+ *          device looks up the array's device address (cudaGetSymbolAddress, checked); make
+ *          that first call before starting any stream capture;
+ *        - the call itself performs no cudaMalloc / cudaFree and creates no events (it is also
+ *          left out of the stage timings of the profiling hooks for that reason). */
+#define B200S_IDXMAP_STATIC_MAX_PIXELS 2097152
+int b200s_idxmap_forward_static(const B200sIdxmapArgs* args, b200s_stream_t stream);
+
 /* ---- introspection for parity tests: copies one private state array of the last
  *      forward into a device buffer the caller owns. `which` is a B200S_STATE_* id;
  *      returns bytes written or a negative error. */

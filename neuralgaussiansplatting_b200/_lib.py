@@ -164,6 +164,7 @@ SYMBOLS = [
     ("b200s_mark_visible", C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("b200s_idxmap_workspace_size", C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     ("b200s_idxmap_forward", C.c_int, [C.POINTER(IdxmapArgs), C.c_void_p]),
+    ("b200s_idxmap_forward_static", C.c_int, [C.POINTER(IdxmapArgs), C.c_void_p]),
     ("b200s_idxmap_backward", C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("b200s_profile_begin", C.c_int, []),
     ("b200s_profile_end", C.c_int, [C.c_void_p, C.c_void_p]),

@@ -20,6 +20,7 @@ int idxmap_forward_impl(const B200sIdxmapArgs* a, cudaStream_t stream);
 int idxmap_backward_impl(int P, int W, int H, const int32_t* out_idx, const float* grad_feature,
                          float* dL_dfeature_vector, cudaStream_t stream);
 size_t idxmap_workspace_size_impl(int P, int W, int H);
+int idxmap_forward_static_impl(const B200sIdxmapArgs* a, cudaStream_t stream);
 }
 
 // ------------------------------------------------------------------ measurement hooks
@@ -397,6 +398,10 @@ size_t b200s_idxmap_workspace_size(int32_t P, int32_t W, int32_t H) {
 int b200s_idxmap_forward(const B200sIdxmapArgs* args, b200s_stream_t stream) {
     ProfScope ps(B200S_STAGE_IDXMAP, (cudaStream_t)stream);
     return idxmap_forward_impl(args, (cudaStream_t)stream);
+}
+int b200s_idxmap_forward_static(const B200sIdxmapArgs* args, b200s_stream_t stream) {
+    // no stage bracket here: the profiling hooks create events, and this entry point promises to create nothing
+    return idxmap_forward_static_impl(args, (cudaStream_t)stream);
 }
 int b200s_idxmap_backward(int32_t P, int32_t W, int32_t H, const int32_t* out_idx, const float* grad_feature,
                           float* dL_dfeature_vector, b200s_stream_t stream) {

@@ -12,6 +12,7 @@
 // which a 64-bit atomicMin z-buffer computes with no sort at all (8 B/pixel instead of
 // ~200 B/instance of sort traffic) and with identical tie-breaking.
 
+#include <mutex>
 #include "kernels.cuh"
 
 namespace b200s {
@@ -213,6 +214,81 @@ int idxmap_backward_impl(int P, int W, int H, const int32_t* out_idx, const floa
     count_launch();
     idx_feature_backward_kernel<<<blocks, 256, 0, stream>>>(P, npix, out_idx, grad_feature, dL_dfeature_vector);
     return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// idxmap forward for callers that have no workspace to give (b200s_idxmap_forward_static).
+//
+// The regular entry point needs an 8-byte-per-pixel z-buffer from the caller. Some hosts cannot
+// produce one: a render loop living inside an application whose device memory is already handed
+// out in full to another allocator (a pre-sized arena, a framework pool capped at a memory
+// fraction), or a loop that must never hit cudaMalloc's device-wide synchronisation. For those the
+// z-buffer below is part of the library image: every GPU that loads libb200splat.so carries these
+// 16 MiB until the process exits, whether or not the entry point is ever called.
+//
+// The array is shared by every call on a device and keeps what the previous call left in it; each
+// call therefore refills the part it uses with the "empty" pattern before splatting. Two calls that
+// overlap on one GPU (different streams, different host threads) would splat into the same pixels
+// and corrupt each other: callers must serialise them.
+constexpr int64_t IDX_STATIC_MAX_PIXELS = B200S_IDXMAP_STATIC_MAX_PIXELS;
+static __device__ __align__(256) unsigned long long g_idx_static_zbuf[IDX_STATIC_MAX_PIXELS];
+
+// In host code `g_idx_static_zbuf` is only a handle for the runtime, not an address a kernel may
+// dereference; the device address is asked for once per device (with that device current) and
+// remembered. cudaGetSymbolAddress may initialise the module on that device, which is why the first
+// call per device is documented as the set-up call.
+constexpr int IDX_STATIC_MAX_DEVICES = 64;
+static std::mutex g_idx_static_mu;
+static unsigned long long* g_idx_static_ptr[IDX_STATIC_MAX_DEVICES] = {};
+
+static int idx_static_zbuf_of_current_device(unsigned long long** out) {
+    int dev = -1;
+    B200S_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= IDX_STATIC_MAX_DEVICES) return B200S_E_UNSUPPORTED;
+    std::lock_guard<std::mutex> lk(g_idx_static_mu);
+    if (g_idx_static_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        B200S_CUDA_OK(cudaGetSymbolAddress(&p, g_idx_static_zbuf));
+        if (p == nullptr) return B200S_E_INTERNAL;
+        g_idx_static_ptr[dev] = (unsigned long long*)p;
+    }
+    *out = g_idx_static_ptr[dev];
+    return 0;
+}
+
+int idxmap_forward_static_impl(const B200sIdxmapArgs* a, cudaStream_t stream) {
+    if (!a) return B200S_E_BADARG;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0) return B200S_E_BADARG;
+    if (!a->out_idx || !a->out_color || !a->out_depth || !a->out_feature) return B200S_E_BADARG;
+    const size_t npix = (size_t)a->W * a->H;
+    // the size limit is checked before anything is enqueued, so a refused call leaves every output untouched
+    if ((int64_t)npix > IDX_STATIC_MAX_PIXELS) return B200S_E_WORKSPACE;
+    if (a->W > 32767 || a->H > 65535) return B200S_E_UNSUPPORTED;
+    if (a->num_rendered_dev) B200S_CUDA_OK(cudaMemsetAsync(a->num_rendered_dev, 0, 4, stream));
+    if (a->P == 0) {   // same zero-filled maps as the workspace variant; the z-buffer is not needed
+        B200S_CUDA_OK(cudaMemsetAsync(a->out_idx, 0, 4 * npix, stream));
+        B200S_CUDA_OK(cudaMemsetAsync(a->out_color, 0, 12 * npix, stream));
+        B200S_CUDA_OK(cudaMemsetAsync(a->out_depth, 0, 4 * npix, stream));
+        B200S_CUDA_OK(cudaMemsetAsync(a->out_feature, 0, 4 * (size_t)NFEAT * npix, stream));
+        return 0;
+    }
+    if (!a->means3D || !a->viewmatrix || !a->projmatrix || !a->campos || !a->feature_vector || !a->radii)
+        return B200S_E_BADARG;
+    unsigned long long* zbuf = nullptr;
+    const int rc = idx_static_zbuf_of_current_device(&zbuf);
+    if (rc) return rc;
+    // the previous call's winners are still in the array: every pixel of this view starts empty again
+    B200S_CUDA_OK(cudaMemsetAsync(zbuf, 0xff, 8 * npix, stream));
+    count_launch();
+    idx_splat_kernel<<<(a->P + 255) / 256, 256, 0, stream>>>(a->P, a->W, a->H, a->means3D, a->viewmatrix,
+                                                           a->projmatrix, a->radii, zbuf, a->num_rendered_dev);
+    B200S_AFTER_LAUNCH(stream, a->debug);
+    const unsigned blocks = (unsigned)((npix + 255) / 256);
+    count_launch();
+    idx_resolve_kernel<<<blocks, 256, 0, stream>>>(a->P, a->W, a->H, zbuf, a->means3D, a->campos, a->feature_vector,
+                                                   a->out_idx, a->out_color, a->out_depth, a->out_feature);
+    B200S_AFTER_LAUNCH(stream, a->debug);
+    return 0;
 }
 
 }  // namespace b200s

@@ -85,6 +85,7 @@ def test_argument_errors_without_a_device(lib):
     assert lib.b200s_forward(None, None) == -1
     assert lib.b200s_backward(None, None) == -1
     assert lib.b200s_idxmap_forward(None, None) == -1
+    assert lib.b200s_idxmap_forward_static(None, None) == -1
     a = _lib.ForwardArgs()
     a.P, a.W, a.H = 10, 0, 16
     assert lib.b200s_forward_preprocess(C.byref(a), None) == -1          # W <= 0
