@@ -314,6 +314,7 @@ int b200s_backward(const B200sBackwardArgs* a, b200s_stream_t stream_) {
     if (has_sr == (a->cov3D_precomp != nullptr)) return B200S_E_BADARG;
     if (a->num_rendered < 0 || a->num_rendered > a->bin_capacity) return B200S_E_BADARG;
     if (a->num_rendered > 0 && !a->bin_ws) return B200S_E_BADARG;
+    if (a->blend_mode != 0 && a->blend_mode != 1) return B200S_E_BADARG;   // same domain as the forward's check
     if (a->bwd_bytes < b200s_backward_workspace_size(a->P, a->deterministic ? a->num_rendered : 0))
         return B200S_E_WORKSPACE;
     if (a->dL_drotations && (reinterpret_cast<uintptr_t>(a->dL_drotations) & 15)) return B200S_E_BADARG;

@@ -34,6 +34,7 @@
 //    needed between the stages (the reference blocks on a 4-byte D2H, rasterizer_impl.cu:281).
 
 #include <cstdlib>
+#include <atomic>
 #include "kernels.cuh"
 
 namespace b200s {
@@ -1114,7 +1115,17 @@ int launch_bwd_prologue(void* zero, size_t zero_bytes, const int* radii, int P, 
     // zero_bytes is a multiple of 16 and `zero` 256-byte aligned (workspace carving); radii != NULL: rows of
     // ACC_STRIDE floats indexed by Gaussian, only the visible ones are cleared
     count_launch();
-    const int blocks = 148 * 2 + (order != nullptr ? 1 : 0);
+    // two fill blocks per SM of the current device (148 SMs on B200), asked for once per device
+    static std::atomic<int> sms_of[64];
+    int dev = 0;
+    B200S_CUDA_OK(cudaGetDevice(&dev));
+    int sms = dev >= 0 && dev < 64 ? sms_of[dev].load(std::memory_order_relaxed) : 0;
+    if (sms <= 0) {
+        B200S_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        if (sms <= 0) sms = 148;
+        if (dev >= 0 && dev < 64) sms_of[dev].store(sms, std::memory_order_relaxed);
+    }
+    const int blocks = sms * 2 + (order != nullptr ? 1 : 0);
     bwd_prologue_kernel<<<blocks, TO_THREADS, 0, stream>>>(reinterpret_cast<float4*>(zero), zero_bytes / 16, radii, P,
                                                            ranges, tile_last, tiles, order);
     return (int)cudaGetLastError();

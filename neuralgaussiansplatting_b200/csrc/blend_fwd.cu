@@ -48,6 +48,7 @@ blend_fwd_kernel(const __grid_constant__ BlendFwdParams p) {
     __shared__ uint16_t s_idx[BATCH];          // tile-level survivors of the batch, list order
     __shared__ int s_cnt[NSEG];
 #if B200S_FWD_BLOCKLISTS
+    static_assert(BATCH <= 256, "s_blk stores entry indices in 8 bits");
     __shared__ uint8_t s_blk[NW][PX][BATCH];   // per pixel block: entry indices of the survivors that reach it
 #endif
 

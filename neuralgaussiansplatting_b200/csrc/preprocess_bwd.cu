@@ -335,7 +335,9 @@ preprocess_bwd_kernel(const __grid_constant__ PreprocessBwdParams p) {
                 const float* sh = p.shs + (int64_t)idx * p.M * 3;
                 const float3 dd = sh_backward(
                     p.D, dir.x, dir.y, dir.z, dRGB, [&](int k) { return f3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]); },
-                    [&](int k, float3 g) { if (write_rows) { out[3 * k] = g.x; out[3 * k + 1] = g.y; out[3 * k + 2] = g.z; } });
+                    // sh_backward offers all 16 coefficients; a row of this tensor holds only M of them (M = 1 / 4 / 9 for
+                    // models trained at --sh_degree 0 / 1 / 2) and has been zeroed above
+                    [&](int k, float3 g) { if (write_rows && k < p.M) { out[3 * k] = g.x; out[3 * k + 1] = g.y; out[3 * k + 2] = g.z; } });
                 const float3 vv = dir_orig;
                 const float sum2 = vv.x * vv.x + vv.y * vv.y + vv.z * vv.z;
                 const float inv = 1.0f / sqrtf(sum2 * sum2 * sum2);

@@ -104,7 +104,7 @@ def render_batch(cameras: Sequence, pc, pipe, bg_color: torch.Tensor, scaling_mo
     needs_grad = torch.is_grad_enabled() and any(
         t is not None and t.requires_grad for t in (pc.get_xyz, pc.get_features, pc.get_opacity, pc.get_scaling,
                                                     pc.get_rotation))
-    if cameras and len(sizes) == 1 and not needs_grad and not pipe.debug:
+    if cameras and len(sizes) == 1 and not needs_grad and not pipe.debug and not pipe.convert_SHs_python:
         from . import _C
         H, W = next(iter(sizes))
         E = torch.Tensor([])
@@ -115,8 +115,6 @@ def render_batch(cameras: Sequence, pc, pipe, bg_color: torch.Tensor, scaling_mo
             cov = pc.get_covariance(scaling_modifier).detach()
         else:
             scales, rots = pc.get_scaling.detach(), pc.get_rotation.detach()
-        if pipe.convert_SHs_python:
-            raise NotImplementedError("render_batch: convert_SHs_python makes colours per view; use render() per view")
         shs = pc.get_features.detach()
         nums, img, radii = _C.rasterize_gaussians_batch(
             bg_color, xyz, colors, pc.get_opacity.detach(), scales, rots, scaling_modifier, cov,

@@ -92,6 +92,8 @@ class ViewParallelTrainer:
             return out
         self.iteration += 1
         peer = isinstance(self.reducer, parallel.PeerGradientAllReduce)
+        if peer:
+            self._agree_on_view_count(len(cameras))
         total, loss3 = None, None
         for i, (cam, gt) in enumerate(zip(cameras, gt_images)):
             last = i == len(cameras) - 1
@@ -107,12 +109,33 @@ class ViewParallelTrainer:
                 parallel.accumulate_(total, grads)
         if self.reducer is not None:
             if peer:
-                self.reducer.start(total, means3D=self.opt.activated["means3D"], sh_degree=self.sh_degree)
+                # the collective's layout (factored SH gradient or dense rows) has to be the same on every rank: it is
+                # derived from the agreed view count, never from what this rank's backward happened to do
+                self.reducer.start(total, means3D=self.opt.activated["means3D"], sh_degree=self.sh_degree,
+                                   factored=self.reducer.factored and len(cameras) == 1)
             else:
                 self.reducer.start(total)
             self.reducer.wait()
         self.opt.step(total)
         return loss3
+
+    def _agree_on_view_count(self, n: int) -> None:
+        """Every rank of a peer-memory group must rasterize the same number of views per step (one view: factored SH
+        gradient; several: dense rows). The first step checks it across ranks (one small all-reduce + host read);
+        afterwards a rank that deviates from the agreed count fails here, before it can join the collective with a
+        different buffer layout than its peers."""
+        agreed = getattr(self, "_views_per_step", None)
+        if agreed is None:
+            t = torch.tensor([n, -n], device=self.dev, dtype=torch.int32)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
+            lo, hi = int(t[0].item()), -int(t[1].item())
+            if lo != hi:
+                raise RuntimeError(f"view-parallel step: ranks rasterize between {lo} and {hi} views this step; "
+                                   "every rank must pass the same number of cameras")
+            self._views_per_step = n
+        elif n != agreed:
+            raise RuntimeError(f"view-parallel step: {n} views on rank {self.rank}, but the group agreed on {agreed} "
+                               "per rank at its first step")
 
     # ------------------------------------------------------------------ adaptive density control
     def _make_reducer(self):
