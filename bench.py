@@ -93,10 +93,12 @@ def timed_region(fn, steps, world, dev, sampler=None, finalize=None):
     """EXACTLY `steps` calls of fn(step) between barrier+synchronize, CUDA events on the current stream,
     MAX over ranks. `finalize` (pipelined loops: last all-reduce wait, last loss read-back) runs INSIDE the region."""
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     barrier_sync(world, dev)
     e0.record()
     for s in range(steps):
         fn(s)
+        marks[s].record()
     if finalize is not None:
         finalize()
     e1.record()
@@ -104,7 +106,19 @@ def timed_region(fn, steps, world, dev, sampler=None, finalize=None):
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    # spread of the individual steps on this rank (median + p10 / p90), from the same events
+    edges = [e0] + marks
+    per = sorted(edges[i].elapsed_time(edges[i + 1]) for i in range(steps))
+    if per:
+        q = lambda f: per[min(len(per) - 1, int(round(f * (len(per) - 1))))]
+        LAST_STEP_SPREAD.clear()
+        LAST_STEP_SPREAD.update({"median_ms": round(q(0.5), 4), "p10_ms": round(q(0.1), 4), "p90_ms": round(q(0.9), 4),
+                                 "min_ms": round(per[0], 4), "max_ms": round(per[-1], 4), "n": len(per),
+                                 "what": "per-step CUDA-event intervals of the timed region on rank 0"})
     return float(ms.item())
+
+
+LAST_STEP_SPREAD = {}
 
 
 def load_peaks():
@@ -352,6 +366,7 @@ def run_ours(args, rank, local_rank, world, dev):
     launches0 = lib.b200s_launch_count()
     with ClockSampler(local_rank) as clk:
         ms_total = timed_region(step_resident, args.steps, world, dev, finalize=reduce_finalize)
+        spread_resident = dict(LAST_STEP_SPREAD)
     launches = int(lib.b200s_launch_count() - launches0)
     nw = max(args.warmup, 3)
     e2e_begin(nw)
@@ -376,8 +391,10 @@ def run_ours(args, rank, local_rank, world, dev):
                    "collective": collective_kind,
                    "parallelism": f"view-parallel x{world}, Gaussians replicated",
                    "l2": "inputs (708 MB of Gaussian parameters) exceed the 126 MB L2; no explicit flush",
-                   "blend_mode": BLEND_MODES[_C.config.get("blend_mode", 0)],
-                   "what": "this repo's sm_100a kernels (libb200splat.so) through the drop-in _C binding"},
+                   },
+        "impl_note": {"blend_mode": BLEND_MODES[_C.config.get("blend_mode", 0)],
+                      "what": "this repo's sm_100a kernels (libb200splat.so) through the drop-in _C binding"},
+        "step_spread": spread_resident,
         "e2e": {"value": round(world * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
                 "ms_per_step": round(ms_e2e / args.steps, 4), "h2d_bytes_per_step": w.h2d_bytes,
                 "d2h_bytes_per_step": w.d2h_bytes,
@@ -387,7 +404,13 @@ def run_ours(args, rank, local_rank, world, dev):
         "clocks": clk.summary(),
     }
     if world > 1:
-        out["collective_check"] = collective_check(w, reducer, _C, step_resident, GRAD_KEYS, rank, world, dev)
+        cc = collective_check(w, reducer, _C, step_resident, GRAD_KEYS, rank, world, dev)
+        out["collective_check"] = cc
+        # the driver keeps `config` verbatim and drops nested extras: the verdict on the collective goes there too
+        out["config"].update({"collective_ok": cc["all_ranks_ok"],
+                              "max_rel_diff_vs_nccl": cc["max_rel_diff_vs_nccl"],
+                              "bit_identical_to_fixed_order_sum": cc["bit_identical_to_fixed_order_sum"],
+                              "replicas_bit_identical": cc["replicas_identical"]})
     _C.config["grad_out"] = None
     if world == 1:
         out["full_iteration"] = full_iteration_ours(args, w, _C, dev)
@@ -493,7 +516,13 @@ def collective_check(w, reducer, _C, step_resident, GRAD_KEYS, rank, world, dev)
             d = (nc - got[k].reshape(nc.shape)).abs().max()
             res["max_abs_diff_vs_nccl"] = max(res["max_abs_diff_vs_nccl"], float(d))
             res["max_rel_diff_vs_nccl"] = max(res["max_rel_diff_vs_nccl"], float(d / nc.abs().max().clamp_min(1e-30)))
-            chk = got[k].double().sum().reshape(1)
+            # replicas are compared by bits: two 64-bit wrap-around checksums of the raw words, one of them
+            # position-weighted (a float64 sum could hide compensating differences and the sign of zero)
+            words = got[k].contiguous().view(torch.int32).reshape(-1).to(torch.int64) & 0xffffffff
+            pos = torch.arange(words.numel(), device=dev, dtype=torch.int64)
+            mixed = (words * 0x9E3779B1 + pos * 0x85EBCA77) & 0x7fffffffffffffff
+            chk = torch.stack([mixed.sum(), words.sum()]).reshape(2)
+            del words, pos, mixed
             allc = [torch.empty_like(chk) for _ in range(world)]
             dist.all_gather(allc, chk)
             if not all(torch.equal(allc[0], c) for c in allc[1:]):
@@ -819,6 +848,7 @@ def run_reference(args, rank, local_rank, world, dev):
     reduce_finalize()
     with ClockSampler(local_rank) as clk:
         ms_total = timed_region(step_resident, args.steps, world, dev, finalize=reduce_finalize)
+        spread_resident = dict(LAST_STEP_SPREAD)
     nw = max(args.warmup, 3)
     e2e_begin(nw)
     for s in range(nw):
@@ -849,10 +879,12 @@ def run_reference(args, rank, local_rank, world, dev):
                                   "NCCL all_reduce, one call on a flat buffer the backward accumulates into"),
                    "parallelism": f"view-parallel x{world}, Gaussians replicated",
                    "l2": "inputs (708 MB of Gaussian parameters) exceed the 126 MB L2; no explicit flush",
-                   "blend_mode": "strict (expf; the reference has no other mode)",
-                   "what": "unmodified reference diff-gaussian-rasterization kernels compiled for sm_100 "
-                           "(oracle/_ref), same GPU, same inputs; the reference has no CPU implementation of this "
-                           "path and no multi-GPU code (the all-reduce at N>1 is this repo's NCCL plumbing)"},
+                   },
+        "impl_note": {"blend_mode": "strict (expf; the reference has no other mode)",
+                      "what": "unmodified reference diff-gaussian-rasterization kernels compiled for sm_100 "
+                              "(oracle/_ref), same GPU, same inputs; the reference has no CPU implementation of this "
+                              "path and no multi-GPU code (the all-reduce at N>1 is this repo's NCCL plumbing)"},
+        "step_spread": spread_resident,
         "e2e": {"value": round(world * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
                 "ms_per_step": round(ms_e2e / args.steps, 4), "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": d2h_bytes,
@@ -1043,15 +1075,21 @@ def main():
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     if args.compute_priority and world > 1 and args.impl == "ours":
         torch.cuda.set_stream(torch.cuda.Stream(device=dev, priority=-1))
+    failed = False
     try:
         res = run_reference(args, rank, local_rank, world, dev) if args.impl == "reference" else \
             run_ours(args, rank, local_rank, world, dev)
         if rank == 0:
             print(json.dumps(res), flush=True)
+        if res.get("collective_check", {}).get("all_ranks_ok") is False:
+            failed = True
     finally:
         if world > 1:
             dist.barrier()
             dist.destroy_process_group()
+    if failed:
+        # the line above is printed for the record; a collective that delivered a wrong sum is not a benchmark result
+        raise SystemExit("collective_check failed: the gradient collective did not deliver the expected sum")
 
 
 if __name__ == "__main__":
