@@ -412,8 +412,7 @@ def run_ours(args, rank, local_rank, world, dev):
                               "bit_identical_to_fixed_order_sum": cc["bit_identical_to_fixed_order_sum"],
                               "replicas_bit_identical": cc["replicas_identical"]})
     _C.config["grad_out"] = None
-    if world == 1:
-        out["full_iteration"] = full_iteration_ours(args, w, _C, dev)
+    out["full_iteration"] = full_iteration_ours(args, w, _C, dev, reducer=reducer, world=world)
     if rank == 0:
         out.update(roofline_pass(args, w, lib, _C, lambda s: step_resident(s, collective=False)))
         if world == 1 and args.blend_mode == "strict":
@@ -543,10 +542,14 @@ def collective_check(w, reducer, _C, step_resident, GRAD_KEYS, rank, world, dev)
 
 
 
-def full_iteration_ours(args, w, _C, dev):
+def full_iteration_ours(args, w, _C, dev, reducer=None, world=1):
     """One whole training iteration with this repo's kernels either side of the rasterizer (SURVEY.md §8(f) ranks
     2-3): forward -> fused L1+SSIM loss and dL/dimage (loss.py) -> backward -> fused activation-backward + Adam +
-    activation (optimizer.py). Device-resident ground truth; informational, the headline metric stays fwd+bwd."""
+    activation (optimizer.py). Device-resident ground truth; informational, the headline metric stays fwd+bwd.
+    N > 1 (BASELINE.json configs[4]): the SYNCHRONOUS view-parallel iteration, every rank one view — the gradient
+    collective completes before Adam and nothing is carried into the next iteration, as the reference's loop orders it
+    (train.py:86-93,127-128). This is the number the overlapped headline metric does not show."""
+    from neuralgaussiansplatting_b200 import parallel
     from neuralgaussiansplatting_b200.loss import fused_l1_ssim
     from neuralgaussiansplatting_b200.optimizer import FusedGaussianAdam
     s, cfg = w.scene, w.cfg
@@ -568,19 +571,42 @@ def full_iteration_ours(args, w, _C, dev):
         g = _C.rasterize_gaussians_backward(fa[0], fa[1], out[2], fa[2], fa[4], fa[5], fa[6], fa[7], fa[8], fa[9],
                                             fa[10], fa[11], dL, fa[14], fa[15], fa[16], out[3], out[0], out[4],
                                             out[5], False)
-        opt.step({"means3D": g[3], "opacities": g[2], "shs": g[5], "scales": g[6], "rotations": g[7]})
+        grads = {"means3D": g[3], "opacities": g[2], "shs": g[5], "scales": g[6], "rotations": g[7]}
+        if reducer is not None:
+            if is_peer:
+                reducer.start(grads, means3D=a["means3D"], sh_degree=3)
+            else:
+                reducer.start(grads)
+            reducer.wait()                       # Adam below consumes the summed gradients: nothing stays in flight
+        opt.step(grads)
 
-    for i in range(max(args.warmup, 3)):
-        step(i)
-    ms = timed_region(step, args.steps, 1, dev)
-    return {"ms_per_step": round(ms / args.steps, 4), "iterations_per_s": round(args.steps / (ms * 1e-3), 2),
-            "what": "rasterizer fwd + fused L1/SSIM loss (value+grad) + rasterizer bwd + fused activation/Adam step, "
-                    "lambda_dssim 0.2, reference learning rates; all b200splat kernels"}
+    is_peer = isinstance(reducer, parallel.PeerGradientAllReduce)
+    saved = _C.config["grad_out"]
+    try:
+        # the backward writes straight into the collective's buffers, as in the headline loop
+        _C.config["grad_out"] = reducer.grad_out if reducer is not None else None
+        for i in range(max(args.warmup, 3)):
+            step(i)
+        ms = timed_region(step, args.steps, world, dev)
+    finally:
+        _C.config["grad_out"] = saved
+    res = {"ms_per_step": round(ms / args.steps, 4), "iterations_per_s": round(args.steps / (ms * 1e-3), 2),
+           "what": "rasterizer fwd + fused L1/SSIM loss (value+grad) + rasterizer bwd + fused activation/Adam step, "
+                   "lambda_dssim 0.2, reference learning rates; all b200splat kernels"}
+    if world > 1:
+        res.update(views_per_iteration=world, views_per_s=round(world * args.steps / (ms * 1e-3), 2),
+                   step_spread=dict(LAST_STEP_SPREAD),
+                   replicas_in_sync=bool(parallel.replicas_in_sync(list(raw.values()))))
+        res["what"] += ("; synchronous view-parallel iteration: one view per rank, the gradient collective finishes "
+                        "before Adam, no overlap across iterations; max over ranks")
+    return res
 
 
-def full_iteration_reference(args, w, ref, kw_of, BK, dev):
+def full_iteration_reference(args, w, ref, kw_of, BK, dev, reducer=None, world=1):
     """The same iteration as the reference runs it: its rasterizer kernels, utils/loss_utils.py's torch expression
-    (cuDNN depthwise convs + autograd), torch activations + autograd + torch.optim.Adam(eps=1e-15)."""
+    (cuDNN depthwise convs + autograd), torch activations + autograd + torch.optim.Adam(eps=1e-15). N > 1: one view
+    per rank and ONE flat ncclAllReduce of the five gradient tensors (the backward accumulates into the flat
+    buffer's views) that completes before the optimizer step — the synchronous iteration, as in our arm."""
     import torch.nn.functional as F
     sys.path.insert(0, str(ROOT / "oracle"))
     import loss_ref                      # the reference's loss expression in torch ops, executed on the GPU here
@@ -604,7 +630,17 @@ def full_iteration_reference(args, w, ref, kw_of, BK, dev):
         x = color.detach().requires_grad_(True)
         loss = 0.8 * loss_ref.l1(x, gts[v]) + 0.2 * (1.0 - loss_ref.ssim(x, gts[v]))
         loss.backward()
-        g = ref.backward(radii=radii, dL_dpix=x.grad, sync=False, **{k: kw[k] for k in BK})
+        gv = None
+        if reducer is not None:
+            v_ = reducer.grad_out()
+            gv = {"means3D": v_["means3D"], "opacity": v_["opacities"], "sh": v_["shs"], "scales": v_["scales"],
+                  "rotations": v_["rotations"]}
+        g = ref.backward(radii=radii, dL_dpix=x.grad, sync=False, **({"out": gv} if gv is not None else {}),
+                         **{k: kw[k] for k in BK})
+        if reducer is not None:
+            reducer.start({"means3D": g["means3D"], "opacities": g["opacity"], "shs": g["sh"], "scales": g["scales"],
+                           "rotations": g["rotations"]})
+            reducer.wait()
         torch.autograd.backward([acts["means3D"], acts["shs"], acts["opacities"], acts["scales"], acts["rotations"]],
                                 [g["means3D"], g["sh"].reshape(acts["shs"].shape), g["opacity"].reshape(-1, 1),
                                  g["scales"], g["rotations"]])
@@ -613,10 +649,16 @@ def full_iteration_reference(args, w, ref, kw_of, BK, dev):
 
     for i in range(max(args.warmup, 3)):
         step(i)
-    ms = timed_region(step, args.steps, 1, dev)
-    return {"ms_per_step": round(ms / args.steps, 4), "iterations_per_s": round(args.steps / (ms * 1e-3), 2),
-            "what": "reference rasterizer kernels + utils/loss_utils.py torch expression + torch autograd through the "
-                    "activations + torch.optim.Adam(eps=1e-15), same learning rates"}
+    ms = timed_region(step, args.steps, world, dev)
+    res = {"ms_per_step": round(ms / args.steps, 4), "iterations_per_s": round(args.steps / (ms * 1e-3), 2),
+           "what": "reference rasterizer kernels + utils/loss_utils.py torch expression + torch autograd through the "
+                   "activations + torch.optim.Adam(eps=1e-15), same learning rates"}
+    if world > 1:
+        res.update(views_per_iteration=world, views_per_s=round(world * args.steps / (ms * 1e-3), 2),
+                   step_spread=dict(LAST_STEP_SPREAD))
+        res["what"] += ("; synchronous view-parallel iteration: one view per rank, one flat NCCL all-reduce that "
+                        "finishes before Adam; max over ranks")
+    return res
 
 
 def ncu_traffic(stage):
@@ -856,7 +898,7 @@ def run_reference(args, rank, local_rank, world, dev):
     e2e_finalize()
     e2e_begin(args.steps)
     ms_e2e = timed_region(step_e2e, args.steps, world, dev, finalize=e2e_finalize)
-    full_it = full_iteration_reference(args, w, ref, kw_of, BK, dev) if world == 1 else None
+    full_it = full_iteration_reference(args, w, ref, kw_of, BK, dev, reducer=reducer, world=world)
     ref.close()
     value = round(world * args.steps / (ms_total * 1e-3), 3)
     workload_name = (f"{cfg.name}: {w.P} Gaussians SH3, {cfg.width}x{cfg.height}, fwd+bwd, 1 view/step/GPU "

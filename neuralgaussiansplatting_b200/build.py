@@ -83,7 +83,46 @@ def build(force: bool = False, verbose: bool = False, extra_flags=(), tag: str =
             print(f"==== {k}\n{v}", file=sys.stderr)
     if logs:
         (obj_dir / "ptxas.log").write_text("".join(f"==== {k}\n{v}\n" for k, v in logs.items()))
+    if not tag and len(logs) == len(SOURCES) and not extra_flags and not os.environ.get("B200S_NVCC_EXTRA"):
+        # a full build of the product library refreshes the committed resource record, so it cannot go stale
+        try:
+            write_ptxas_record(logs, PKG_DIR.parent / "profiles" / "ptxas_current.txt")
+        except OSError:
+            pass
     return lib_path
+
+
+def write_ptxas_record(logs, path: Path) -> None:
+    """One line per kernel from `-Xptxas -v`: registers, spill bytes, static shared memory (no compile times, so the
+    file only changes when the code generation does). Kernels that spill are listed again at the end."""
+    import re
+    rows, spills = [], []
+    for src in SOURCES:
+        name = None
+        stack = st = ld = 0
+        for line in logs.get(src, "").splitlines():
+            m = re.search(r"Function properties for (\S+)", line)
+            if m:
+                name = m.group(1)
+                continue
+            m = re.search(r"(\d+) bytes stack frame, (\d+) bytes spill stores, (\d+) bytes spill loads", line)
+            if m:
+                stack, st, ld = map(int, m.groups())
+                continue
+            m = re.search(r"Used (\d+) registers", line)
+            if m and name:
+                sm = re.search(r"(\d+) bytes smem", line)
+                regs, smem = int(m.group(1)), int(sm.group(1)) if sm else 0
+                r = subprocess.run(["c++filt", "-p", name], capture_output=True, text=True)
+                nice = r.stdout.strip() if r.returncode == 0 and r.stdout.strip() else name
+                rows.append(f"{src:20s} {regs:4d} regs {smem:6d} B smem {stack:4d} B stack {st:4d} B spill st {ld:4d} B spill ld  {nice}")
+                if st or ld:
+                    spills.append(rows[-1])
+                name = None
+    path.parent.mkdir(exist_ok=True)
+    path.write_text("# written by neuralgaussiansplatting_b200/build.py on every full build of libb200splat.so "
+                    "(nvcc -Xptxas -v, sm_100a)\n" + "\n".join(rows) + "\n\n# kernels that spill: "
+                    + (str(len(spills)) + "\n" + "\n".join(spills) if spills else "none") + "\n")
 
 
 if __name__ == "__main__":

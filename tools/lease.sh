@@ -51,10 +51,10 @@ ncu_aux)
     timeout 300 python tools/idxmap_times.py --cfg C3 --steps 2 > gpurun_out/${T}_idxmap_times.jsonl 2>&1 || { echo "idxmap target failed without ncu"; continue; }
     timeout 300 python tools/step_parts.py > gpurun_out/${T}_step_parts.json 2>&1 || { echo "step_parts target failed without ncu"; continue; }
     timeout 300 python tools/time_reconstruct.py > gpurun_out/${T}_reconstruct.jsonl 2>&1 || echo "reconstruct target failed without ncu"
-    timeout 900 ncu --set full --clock-control none --import-source on -f -o gpurun_out/${T}_idx -k regex:"idx_" --launch-skip 6 -c 3 \
+    timeout 900 ncu --set full --clock-control none --import-source on -f -o gpurun_out/${T}_idx -k regex:"idx_" --launch-skip 10 -c 3 \
         python tools/idxmap_times.py --cfg C3 --steps 2 > gpurun_out/${T}_ncu_idx.log 2>&1; echo "ncu idx rc=$?"
     summarise gpurun_out/${T}_idx idxmap_C3 idx_splat idx_resolve idx_feature_backward
-    timeout 900 ncu --set full --clock-control none --import-source on -f -o gpurun_out/${T}_aux -k regex:"adam_step|loss_fwd|loss_bwd" --launch-skip 9 -c 3 \
+    timeout 900 ncu --set full --clock-control none --import-source on -f -o gpurun_out/${T}_aux -k regex:"adam_step|loss_fwd|loss_bwd" --launch-skip 48 -c 6 \
         python tools/step_parts.py > gpurun_out/${T}_ncu_aux.log 2>&1; echo "ncu adam/loss rc=$?"
     summarise gpurun_out/${T}_aux adam_loss_C3 adam_step loss_fwd loss_bwd
     timeout 900 ncu --set full --clock-control none --import-source on -f -o gpurun_out/${T}_shr -k regex:"sh_grad_reconstruct" --launch-skip 3 -c 2 \
