@@ -129,17 +129,28 @@ idx_resolve_kernel(int P, int W, int H, const unsigned long long* __restrict__ z
         }
     }
     __syncwarp();
-    for (int q = 0; q < 32; ++q) {
-        const int64_t pq = pix0 + q;
-        if (pq >= npix) break;
-        const int gq = s_g[warp][q];
-        float v0 = 0.f, v1 = 0.f;      // channels lane and lane+32
-        if (gq >= 0) {
-            v0 = lane < FEAT_FIRST_LEARNED ? s_enc[warp][q][lane] : feature_vector[(size_t)gq * NFEAT + lane];
-            v1 = feature_vector[(size_t)gq * NFEAT + 32 + lane];
+    // four pixels per trip: their eight gathers are issued together before the first store needs its data
+    // (the plain one-pixel loop sat on `long_scoreboard` at the store, profiles/r03d_ncu_stalls_idxmap_C3.txt)
+    for (int q0 = 0; q0 < 32; q0 += 4) {
+        if (pix0 + q0 >= npix) break;
+        float v0[4], v1[4];            // channels lane and lane+32 of pixels q0..q0+3
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gq = s_g[warp][q0 + j];
+            v0[j] = 0.f; v1[j] = 0.f;
+            if (gq >= 0) {             // pixels past the end of the image carry g = -1
+                v0[j] = lane < FEAT_FIRST_LEARNED ? s_enc[warp][q0 + j][lane] : __ldg(&feature_vector[(size_t)gq * NFEAT + lane]);
+                v1[j] = __ldg(&feature_vector[(size_t)gq * NFEAT + 32 + lane]);
+            }
         }
-        out_feature[(size_t)pq * NFEAT + lane] = v0;
-        out_feature[(size_t)pq * NFEAT + 32 + lane] = v1;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int64_t pq = pix0 + q0 + j;
+            if (pq < npix) {
+                out_feature[(size_t)pq * NFEAT + lane] = v0[j];
+                out_feature[(size_t)pq * NFEAT + 32 + lane] = v1[j];
+            }
+        }
     }
 }
 
