@@ -731,6 +731,10 @@ def roofline_pass(args, w, lib, _C, step_fn):
                          "unit": "G warp-inst/s", "frac": round(ach / sm_peaks["issue_ginst_per_s"], 4),
                          "what": "smsp__inst_executed.sum of the committed ncu capture / the live launch time, against "
                                  f"the issue-slot peak {sm_src}"}
+        # the same rate against the hardware's 4 issue slots per clock and SM at the nominal maximum clock
+        hw_slots = 148 * 4 * 1965.0e6 / 1e9
+        roof["issue"]["hw_slot_peak"] = round(hw_slots, 1)
+        roof["issue"]["frac_of_hw_slots"] = round(ach / hw_slots, 4)
     return {"roofline": roof, "stages": rows,
             "workload_counts": {"P": w.P, "P_visible": P_vis, "num_rendered": N, "pairs_traversed_fwd": counts[0],
                                 "pairs_contributing": counts[1], "pairs_traversed_bwd": counts[2]}}
